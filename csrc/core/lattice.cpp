@@ -1,0 +1,582 @@
+#include "lattice.h"
+#include "common.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cuda_runtime.h>
+
+namespace tclb {
+
+Box Box::intersect(const Box &o) const {
+    Box r;
+    r.x0 = std::max(x0, o.x0); r.y0 = std::max(y0, o.y0); r.z0 = std::max(z0, o.z0);
+    r.nx = std::min(x0 + nx, o.x0 + o.nx) - r.x0;
+    r.ny = std::min(y0 + ny, o.y0 + o.ny) - r.y0;
+    r.nz = std::min(z0 + nz, o.z0 + o.nz) - r.z0;
+    if (r.nx < 0) r.nx = 0;
+    if (r.ny < 0) r.ny = 0;
+    if (r.nz < 0) r.nz = 0;
+    return r;
+}
+
+// ------------------------------------------------------------------------------------------
+Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &local, const int total[3])
+    : model(m), backend(backend_), device(device_), rank(rank_), region(local), cur(0), iter(0), reset_iter(0), epoch(0),
+      halo_mode(TCLB_HALO_DIRECT), sig_enable(false), stream(nullptr), arena_(backend_, device_), zone_dev_(nullptr),
+      zone_dev_bytes_(0), zone_stride_(1), cuts_dev_(nullptr), st_dev_(nullptr), st_n_(0), scratch_(nullptr), scratch_bytes_(0) {
+    tot[0] = total[0]; tot[1] = total[1]; tot[2] = total[2];
+    nx = local.nx; ny = local.ny; nz = local.nz;
+    gy = m->d->gy; gz = m->d->gz;
+    NY = ny + 2 * gy; NZ = nz + 2 * gz;
+    plane_elems = (size_t)nx * NY * NZ;
+    snap_bytes = plane_elems * m->d->n_fields * m->real_size();
+    int s0 = arena_.reserve(snap_bytes, "snapshot0");
+    int s1 = arena_.reserve(snap_bytes, "snapshot1");
+    int sf = arena_.reserve(plane_elems * m->flag_size(), "flags");
+    int sg = arena_.reserve(sizeof(double) * std::max(1, m->d->n_globals), "globals");
+    int ss = arena_.reserve(sizeof(unsigned) * 64, "halo flags");
+    arena_.finalize();
+    snap_[0] = arena_.ptr(s0); snap_[1] = arena_.ptr(s1);
+    flags_ = arena_.ptr(sf);
+    globals_dev_ = (double *)arena_.ptr(sg);
+    sig_ = (unsigned *)arena_.ptr(ss);
+    settings.assign(std::max(1, m->d->n_settings), 0.0);
+    globals.assign(std::max(1, m->d->n_globals), 0.0);
+    zs.configure(m->d->n_zonesettings, m->d->zone_max + 1);
+    if (backend == TCLB_BACKEND_CUDA) {
+        TCLB_CUDA(cudaSetDevice(device));
+        cudaStream_t s;
+        TCLB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+        stream = (void *)s;
+    }
+    for (int d = 0; d < TCLB_MAX_NEIGH; d++) halo[d] = HaloTarget();
+}
+
+Lattice::~Lattice() {
+    if (backend == TCLB_BACKEND_CUDA) {
+        cudaSetDevice(device);
+        if (stream) cudaStreamDestroy((cudaStream_t)stream);
+        if (zone_dev_) cudaFree(zone_dev_);
+        if (cuts_dev_) cudaFree(cuts_dev_);
+        if (st_dev_) cudaFree(st_dev_);
+        if (scratch_) cudaFree(scratch_);
+    } else {
+        free(zone_dev_); free(cuts_dev_); free(st_dev_); free(scratch_);
+    }
+}
+
+void Lattice::to_host(void *dst, const void *src, size_t bytes) const {
+    if (backend == TCLB_BACKEND_CUDA) {
+        TCLB_CUDA(cudaSetDevice(device));
+        TCLB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+        TCLB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    } else memcpy(dst, src, bytes);
+}
+void Lattice::to_dev(void *dst, const void *src, size_t bytes) const {
+    if (backend == TCLB_BACKEND_CUDA) {
+        TCLB_CUDA(cudaSetDevice(device));
+        TCLB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+        TCLB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    } else memcpy(dst, src, bytes);
+}
+void Lattice::sync() const {
+    if (backend == TCLB_BACKEND_CUDA) {
+        TCLB_CUDA(cudaSetDevice(device));
+        TCLB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    }
+}
+void *Lattice::scratch(size_t bytes) {
+    if (bytes <= scratch_bytes_) return scratch_;
+    if (backend == TCLB_BACKEND_CUDA) {
+        TCLB_CUDA(cudaSetDevice(device));
+        if (scratch_) TCLB_CUDA(cudaFree(scratch_));
+        TCLB_CUDA(cudaMalloc(&scratch_, bytes));
+    } else {
+        free(scratch_);
+        scratch_ = malloc(bytes);
+    }
+    scratch_bytes_ = bytes;
+    return scratch_;
+}
+void *Lattice::field_ptr(int snap, int field) const {
+    return (char *)snap_[snap] + (size_t)field * plane_elems * model->real_size();
+}
+
+// ---- flags -------------------------------------------------------------------------------
+void Lattice::flag_overwrite(const uint32_t *fl, const Box &b) {
+    const int fs = model->flag_size();
+    std::vector<unsigned char> host(plane_elems * fs);
+    to_host(host.data(), flags_, host.size());
+    for (int z = 0; z < b.nz; z++)
+        for (int y = 0; y < b.ny; y++)
+            for (int x = 0; x < b.nx; x++) {
+                size_t i = ((size_t)(z + b.z0 + gz) * NY + (y + b.y0 + gy)) * nx + (x + b.x0);
+                uint32_t v = fl[((size_t)z * b.ny + y) * b.nx + x];
+                if (fs == 2) ((uint16_t *)host.data())[i] = (uint16_t)v;
+                else ((uint32_t *)host.data())[i] = v;
+            }
+    to_dev(flags_, host.data(), host.size());
+}
+void Lattice::get_flags(const Box &b, uint32_t *out) const {
+    const int fs = model->flag_size();
+    std::vector<unsigned char> host(plane_elems * fs);
+    to_host(host.data(), flags_, host.size());
+    for (int z = 0; z < b.nz; z++)
+        for (int y = 0; y < b.ny; y++)
+            for (int x = 0; x < b.nx; x++) {
+                size_t i = ((size_t)(z + b.z0 + gz) * NY + (y + b.y0 + gy)) * nx + (x + b.x0);
+                out[((size_t)z * b.ny + y) * b.nx + x] = fs == 2 ? ((uint16_t *)host.data())[i] : ((uint32_t *)host.data())[i];
+            }
+}
+void Lattice::cuts_overwrite(const uint16_t *cuts) {
+    size_t bytes = (size_t)26 * plane_elems * sizeof(uint16_t);
+    if (!cuts) return;
+    if (!cuts_dev_) {
+        if (backend == TCLB_BACKEND_CUDA) { TCLB_CUDA(cudaSetDevice(device)); TCLB_CUDA(cudaMalloc(&cuts_dev_, bytes)); }
+        else cuts_dev_ = malloc(bytes);
+    }
+    std::vector<uint16_t> host((size_t)26 * plane_elems, 65535);
+    for (int d = 0; d < 26; d++)
+        for (int z = 0; z < nz; z++)
+            for (int y = 0; y < ny; y++)
+                memcpy(&host[(size_t)d * plane_elems + ((size_t)(z + gz) * NY + (y + gy)) * nx],
+                       &cuts[(((size_t)d * nz + z) * ny + y) * nx], sizeof(uint16_t) * nx);
+    to_dev(cuts_dev_, host.data(), bytes);
+}
+
+// ---- fields ------------------------------------------------------------------------------
+void Lattice::copy_field_out(int field, void *dst) const {
+    const int rs = model->real_size();
+    const char *src = (const char *)field_ptr(cur, field);
+    if (backend == TCLB_BACKEND_CUDA) {
+        TCLB_CUDA(cudaSetDevice(device));
+        for (int z = 0; z < nz; z++)
+            TCLB_CUDA(cudaMemcpyAsync((char *)dst + (size_t)z * ny * nx * rs, src + ((size_t)(z + gz) * NY + gy) * nx * rs,
+                                      (size_t)ny * nx * rs, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+        TCLB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    } else {
+        for (int z = 0; z < nz; z++)
+            memcpy((char *)dst + (size_t)z * ny * nx * rs, src + ((size_t)(z + gz) * NY + gy) * nx * rs, (size_t)ny * nx * rs);
+    }
+}
+void Lattice::copy_field_in(int field, const void *srcv) {
+    const int rs = model->real_size();
+    char *dst = (char *)field_ptr(cur, field);
+    if (backend == TCLB_BACKEND_CUDA) {
+        TCLB_CUDA(cudaSetDevice(device));
+        for (int z = 0; z < nz; z++)
+            TCLB_CUDA(cudaMemcpyAsync(dst + ((size_t)(z + gz) * NY + gy) * nx * rs, (const char *)srcv + (size_t)z * ny * nx * rs,
+                                      (size_t)ny * nx * rs, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+        TCLB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    } else {
+        for (int z = 0; z < nz; z++)
+            memcpy(dst + ((size_t)(z + gz) * NY + gy) * nx * rs, (const char *)srcv + (size_t)z * ny * nx * rs, (size_t)ny * nx * rs);
+    }
+}
+void Lattice::fill_field(int field, double v) {
+    const int rs = model->real_size();
+    std::vector<char> buf((size_t)nz * ny * nx * rs);
+    if (rs == 4) std::fill((float *)buf.data(), (float *)buf.data() + (size_t)nz * ny * nx, (float)v);
+    else std::fill((double *)buf.data(), (double *)buf.data() + (size_t)nz * ny * nx, v);
+    copy_field_in(field, buf.data());
+}
+
+// ---- settings ----------------------------------------------------------------------------
+void Lattice::set_setting(int idx, double v) {
+    // value, then every setting derived from it, transitively (reference Lattice::SetSetting
+    // src/Lattice.cu.Rt:1350-1358 chains the generated DF_<name> functions the same way)
+    int guard = 0;
+    while (idx >= 0 && guard++ < 64) {
+        settings[idx] = v;
+        const tclb_setting_t &s = model->d->settings[idx];
+        if (s.derived_target < 0 || !s.derive) break;
+        v = s.derive(v);
+        idx = s.derived_target;
+    }
+}
+void Lattice::set_synthetic_turbulence(const std::vector<tclb_st_mode_t> &modes) {
+    size_t bytes = modes.size() * sizeof(tclb_st_mode_t);
+    if (backend == TCLB_BACKEND_CUDA) {
+        TCLB_CUDA(cudaSetDevice(device));
+        if (st_dev_) TCLB_CUDA(cudaFree(st_dev_));
+        st_dev_ = nullptr;
+        if (bytes) TCLB_CUDA(cudaMalloc(&st_dev_, bytes));
+    } else {
+        free(st_dev_);
+        st_dev_ = bytes ? malloc(bytes) : nullptr;
+    }
+    if (bytes) to_dev(st_dev_, modes.data(), bytes);
+    st_n_ = (int)modes.size();
+}
+void Lattice::upload_zone_table_if_dirty() {
+    if (!zs.dirty() && zone_dev_) return;
+    int stride = zs.zones();
+    std::vector<double> tab;
+    zs.build_table(tab, stride);
+    const int rs = model->real_size();
+    size_t bytes = std::max<size_t>(tab.size(), 1) * rs;
+    if (bytes > zone_dev_bytes_) {
+        if (backend == TCLB_BACKEND_CUDA) {
+            TCLB_CUDA(cudaSetDevice(device));
+            sync();
+            if (zone_dev_) TCLB_CUDA(cudaFree(zone_dev_));
+            TCLB_CUDA(cudaMalloc(&zone_dev_, bytes));
+        } else {
+            free(zone_dev_);
+            zone_dev_ = malloc(bytes);
+        }
+        zone_dev_bytes_ = bytes;
+    }
+    if (rs == 4) {
+        std::vector<float> f(tab.begin(), tab.end());
+        if (f.empty()) f.push_back(0.f);
+        to_dev(zone_dev_, f.data(), f.size() * 4);
+    } else {
+        if (tab.empty()) tab.push_back(0.0);
+        to_dev(zone_dev_, tab.data(), tab.size() * 8);
+    }
+    zone_stride_ = stride;
+    zs.clear_dirty();
+}
+
+// ---- launches ----------------------------------------------------------------------------
+void Lattice::fill_launch(tclb_launch_t &L) const {
+    memset(&L, 0, sizeof(L));
+    L.backend = backend;
+    L.stream = stream;
+    L.nx = nx; L.ny = ny; L.nz = nz; L.gy = gy; L.gz = gz;
+    L.off_x = region.x0; L.off_y = region.y0; L.off_z = region.z0;
+    L.tot_nx = tot[0]; L.tot_ny = tot[1]; L.tot_nz = tot[2];
+    L.flags = flags_;
+    L.cuts = cuts_dev_;
+    L.globals = globals_dev_;
+    L.settings = settings.data();
+    L.zone_table = zone_dev_;
+    L.zone_len = zs.len();
+    L.zone_index = zs.len() > 1 ? iter % zs.len() : 0;
+    L.zone_stride = zone_stride_;
+    L.iter = iter; L.reset_iter = reset_iter;
+    L.st_modes = (const tclb_st_mode_t *)st_dev_; L.st_n = st_n_;
+    L.block_x = block_x; L.block_y = block_y;
+    L.scale = 1.0;
+}
+void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode) {
+    upload_zone_table_if_dirty();
+    tclb_launch_t L;
+    fill_launch(L);
+    L.snap_in = snap_[in_snap];
+    L.snap_out = snap_[out_snap];
+    L.globals_mode = gmode;
+    L.halo_mode = halo_mode;
+    epoch++;
+    L.sig_epoch = epoch;
+    L.sig_enable = (sig_enable && halo_mode == TCLB_HALO_DIRECT) ? 1 : 0;
+    L.sig_count = sig_ + 9;
+    for (int d = 0; d < TCLB_MAX_NEIGH; d++) {
+        if (d == 4) continue;
+        L.halo_snap[d] = halo[d].snap[out_snap];
+        L.halo_ny[d] = halo[d].ny; L.halo_nz[d] = halo[d].nz;
+        if (L.sig_enable && halo[d].rank != rank && halo[d].rank >= 0) {
+            L.sig_remote[d] = halo[d].flag;
+            L.sig_wait[d] = sig_ + d;
+        }
+    }
+    if (backend == TCLB_BACKEND_CUDA) TCLB_CUDA(cudaSetDevice(device));
+    if (model->d->run_stage(stage, &L) != 0) fail("stage %s failed: %s", model->d->stages[stage].name, model->d->last_error());
+}
+void Lattice::clear_globals() {
+    std::vector<double> z(model->d->n_globals, 0.0);
+    for (int i = 0; i < model->d->n_globals; i++) z[i] = model->d->globals[i].op == TCLB_OP_MAX ? model->d->globals[i].base : 0.0;
+    if (backend == TCLB_BACKEND_CUDA) {
+        TCLB_CUDA(cudaSetDevice(device));
+        TCLB_CUDA(cudaMemcpyAsync(globals_dev_, z.data(), z.size() * sizeof(double), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+        TCLB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));   // z is a stack-local staging buffer
+    } else memcpy(globals_dev_, z.data(), z.size() * sizeof(double));
+}
+void Lattice::fetch_globals() {
+    to_host(globals.data(), globals_dev_, sizeof(double) * model->d->n_globals);
+}
+void Lattice::get_quantity(int q, const Box &b, void *dst, double scale, bool dst_on_device) {
+    upload_zone_table_if_dirty();
+    const int nc = model->d->quantities[q].vector ? 3 : 1;
+    size_t bytes = (size_t)b.size() * nc * model->real_size();
+    tclb_launch_t L;
+    fill_launch(L);
+    L.snap_in = snap_[cur]; L.snap_out = snap_[cur];
+    L.rx = b.x0; L.ry = b.y0; L.rz = b.z0; L.rnx = b.nx; L.rny = b.ny; L.rnz = b.nz;
+    L.scale = scale;
+    bool direct = (backend == TCLB_BACKEND_CPU) || dst_on_device;
+    L.out = direct ? dst : scratch(bytes);
+    if (backend == TCLB_BACKEND_CUDA) TCLB_CUDA(cudaSetDevice(device));
+    if (model->d->get_quantity(q, &L) != 0) fail("quantity %s failed: %s", model->d->quantities[q].name, model->d->last_error());
+    if (!direct) to_host(dst, L.out, bytes);
+}
+void Lattice::color(int zplane, float scale, unsigned char *rgba, bool dst_on_device) {
+    upload_zone_table_if_dirty();
+    size_t bytes = (size_t)nx * ny * 4;
+    tclb_launch_t L;
+    fill_launch(L);
+    L.snap_in = snap_[cur]; L.snap_out = snap_[cur];
+    L.rx = 0; L.ry = 0; L.rz = zplane; L.rnx = nx; L.rny = ny; L.rnz = 1;
+    L.scale = scale;
+    bool direct = (backend == TCLB_BACKEND_CPU) || dst_on_device;
+    L.out = direct ? (void *)rgba : scratch(bytes);
+    if (backend == TCLB_BACKEND_CUDA) TCLB_CUDA(cudaSetDevice(device));
+    if (model->d->color(&L) != 0) fail("colour kernel failed: %s", model->d->last_error());
+    if (!direct) to_host(rgba, L.out, bytes);
+}
+bool Lattice::has_nan(int q, const Box &b) {
+    const int nc = model->d->quantities[q].vector ? 3 : 1;
+    size_t n = (size_t)b.size() * nc;
+    std::vector<char> buf(n * model->real_size());
+    get_quantity(q, b, buf.data(), 1.0);
+    if (model->real_size() == 4) { const float *p = (const float *)buf.data(); for (size_t i = 0; i < n; i++) if (!(p[i] == p[i])) return true; }
+    else { const double *p = (const double *)buf.data(); for (size_t i = 0; i < n; i++) if (!(p[i] == p[i])) return true; }
+    return false;
+}
+void Lattice::save_raw(const std::string &file) const {
+    std::vector<char> buf(snap_bytes);
+    to_host(buf.data(), snap_[cur], snap_bytes);
+    FILE *f = fopen(file.c_str(), "wb");
+    if (!f) fail("cannot write %s", file.c_str());
+    fwrite(buf.data(), 1, buf.size(), f);
+    fclose(f);
+}
+void Lattice::load_raw(const std::string &file) {
+    std::vector<char> buf(snap_bytes);
+    FILE *f = fopen(file.c_str(), "rb");
+    if (!f) fail("cannot read %s", file.c_str());
+    size_t n = fread(buf.data(), 1, buf.size(), f);
+    fclose(f);
+    if (n != buf.size()) fail("%s: expected %zu bytes, got %zu", file.c_str(), buf.size(), n);
+    to_dev(snap_[cur], buf.data(), snap_bytes);
+}
+
+// ------------------------------------------------------------------------------------------
+Decomposition Decomposition::make(int nx, int ny, int nz, int nranks) {
+    Decomposition D;
+    D.nranks = nranks;
+    D.tot[0] = nx; D.tot[1] = ny; D.tot[2] = nz;
+    D.boxes.assign(nranks, Box());
+    float mincom = (1.0f + nranks) * (ny + nz);
+    bool done = false;
+    for (int divz = 1; divz <= nranks; divz++) {
+        if (nranks % divz) continue;
+        int divy = nranks / divz;
+        float com = (float)divz * ny + (float)divy * nz;
+        if (com < mincom) {
+            mincom = com;
+            if (nz >= divz && ny >= divy) {
+                std::vector<int> yl(divy), zl(divz);
+                int my = ny, mz = nz;
+                for (int i = 0; i < divy; i++) { yl[i] = my / (divy - i); my -= yl[i]; }
+                for (int i = 0; i < divz; i++) { zl[i] = mz / (divz - i); mz -= zl[i]; }
+                int k = 0, dz = 0;
+                for (int i = 0; i < divz; i++) {
+                    int dy = 0;
+                    for (int j = 0; j < divy; j++) {
+                        Box &b = D.boxes[k++];
+                        b.x0 = 0; b.nx = nx; b.y0 = dy; b.ny = yl[j]; b.z0 = dz; b.nz = zl[i];
+                        dy += yl[j];
+                    }
+                    dz += zl[i];
+                }
+                D.divy = divy; D.divz = divz;
+                done = true;
+            }
+        }
+    }
+    if (!done) fail("lattice %dx%dx%d is too small to be divided over %d ranks", nx, ny, nz, nranks);
+    return D;
+}
+int Decomposition::neighbour(int rank, int dy, int dz) const {
+    int iy = rank % divy, iz = rank / divy;
+    iy = (iy + dy + divy) % divy;
+    iz = (iz + dz + divz) % divz;
+    return iy + divy * iz;
+}
+
+// ------------------------------------------------------------------------------------------
+Domain::Domain(Model *m, int backend_, int nx, int ny, int nz, int nranks, const std::vector<int> &local_ranks,
+               const std::vector<int> &devices)
+    : model(m), backend(backend_), iter(0), use_direct_halo(true) {
+    dec = Decomposition::make(nx, ny, nz, nranks);
+    lat.assign(nranks, nullptr);
+    local = local_ranks;
+    for (size_t i = 0; i < local.size(); i++) {
+        int r = local[i];
+        int dev = devices.empty() ? 0 : devices[i % devices.size()];
+        lat[r] = new Lattice(m, backend, dev, r, dec.boxes[r], dec.tot);
+    }
+    globals.assign(std::max(1, m->d->n_globals), 0.0);
+    // defaults of the settings are applied by the Solver (needs the unit system)
+    connect_local();
+    finalize_wiring();
+}
+Domain::~Domain() {
+    for (auto *l : lat) delete l;
+}
+static int opposite(int d) {
+    int dy = d % 3 - 1, dz = d / 3 - 1;
+    return (-dy + 1) + 3 * (-dz + 1);
+}
+void Domain::connect_local() {
+    // peer access between the devices of local ranks
+    if (backend == TCLB_BACKEND_CUDA) {
+        for (int a : local)
+            for (int b : local) {
+                int da = lat[a]->device, db = lat[b]->device;
+                if (da == db) continue;
+                int can = 0;
+                TCLB_CUDA(cudaDeviceCanAccessPeer(&can, da, db));
+                if (can) {
+                    TCLB_CUDA(cudaSetDevice(da));
+                    cudaError_t e = cudaDeviceEnablePeerAccess(db, 0);
+                    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) TCLB_CUDA(e);
+                    cudaGetLastError();
+                } else logf(L_WARNING, "device %d cannot access device %d directly; direct halo needs peer access", da, db);
+            }
+    }
+    for (int r : local) {
+        for (int d = 0; d < TCLB_MAX_NEIGH; d++) {
+            if (d == 4) continue;
+            int dy = d % 3 - 1, dz = d / 3 - 1;
+            int nb = dec.neighbour(r, dy, dz);
+            HaloTarget &t = lat[r]->halo[d];
+            t.rank = nb;
+            t.ny = dec.boxes[nb].ny; t.nz = dec.boxes[nb].nz;
+            if (lat[nb]) {
+                t.snap[0] = lat[nb]->snap_ptr(0);
+                t.snap[1] = lat[nb]->snap_ptr(1);
+                t.flag = lat[nb]->flags_in() + opposite(d);
+            }
+        }
+    }
+}
+void Domain::set_remote_target(int rank, int d, const HaloTarget &t) {
+    if (!lat[rank]) fail("set_remote_target: rank %d is not local", rank);
+    lat[rank]->halo[d] = t;
+}
+void Domain::finalize_wiring() {
+    for (int r : local) {
+        bool any_remote_dev = false, all_wired = true;
+        for (int d = 0; d < TCLB_MAX_NEIGH; d++) {
+            if (d == 4) continue;
+            HaloTarget &t = lat[r]->halo[d];
+            if (!t.snap[0]) all_wired = false;
+            if (t.rank != r) any_remote_dev = true;
+        }
+        // sequence flags are only needed between kernels that may run concurrently (different
+        // devices / processes); ranks sharing one stream-ordered device do not need them, and the
+        // CPU oracle runs ranks one after another.
+        bool concurrent = false;
+        if (backend == TCLB_BACKEND_CUDA && any_remote_dev) {
+            for (int d = 0; d < TCLB_MAX_NEIGH; d++) {
+                if (d == 4) continue;
+                int nb = lat[r]->halo[d].rank;
+                if (nb == r) continue;
+                if (!lat[nb] || lat[nb]->device != lat[r]->device) concurrent = true;
+            }
+        }
+        lat[r]->sig_enable = concurrent && all_wired;
+        lat[r]->halo_mode = (use_direct_halo && all_wired) ? TCLB_HALO_DIRECT : TCLB_HALO_NONE;
+    }
+}
+void Domain::set_setting(int idx, double v) { for (int r : local) lat[r]->set_setting(idx, v); }
+void Domain::set_zone_setting(int s, int zone, double v) { for (int r : local) lat[r]->zs.set(s, zone, v); }
+void Domain::set_zone_series(int s, int zone, const std::vector<double> &v) { for (int r : local) lat[r]->zs.set_series(s, zone, v); }
+void Domain::set_zones(int n) { for (int r : local) lat[r]->zs.set_zones(n); }
+void Domain::sync() { for (int r : local) lat[r]->sync(); }
+
+void Domain::copy_exchange(int s) {
+    // Baseline halo path: copy the border rows of every local rank into the ghost rows of its
+    // neighbours with stream-ordered memcpys (plays the role of the reference's
+    // D2H -> MPI_Isend/Irecv -> H2D, src/Lattice.cu.Rt:327-389, without the host bounce).
+    const int rs = model->real_size();
+    const int nf = model->d->n_fields;
+    if (backend == TCLB_BACKEND_CUDA) sync();
+    for (int r : local) {
+        Lattice *A = lat[r];
+        for (int d = 0; d < TCLB_MAX_NEIGH; d++) {
+            if (d == 4) continue;
+            int dy = d % 3 - 1, dz = d / 3 - 1;
+            if ((dy != 0 && A->gy == 0) || (dz != 0 && A->gz == 0)) continue;
+            int nb = A->halo[d].rank;
+            Lattice *Bl = lat[nb];
+            if (!Bl) continue;      // remote: handled by exchange_hook
+            // rows of A that B needs: y in [ny-gy, ny) for dy=+1, [0,gy) for dy=-1, all for 0
+            int ys = dy > 0 ? A->ny - A->gy : 0, yn = dy != 0 ? A->gy : A->ny;
+            int zs_ = dz > 0 ? A->nz - A->gz : 0, zn = dz != 0 ? A->gz : A->nz;
+            for (int f = 0; f < nf; f++)
+                for (int z = 0; z < zn; z++) {
+                    int za = zs_ + z;
+                    int zb = dz > 0 ? za - A->nz : (dz < 0 ? za + Bl->nz : za);
+                    for (int y = 0; y < yn; y++) {
+                        int ya = ys + y;
+                        int yb = dy > 0 ? ya - A->ny : (dy < 0 ? ya + Bl->ny : ya);
+                        const char *src = (const char *)A->field_ptr(s, f) + (((size_t)(za + A->gz) * A->NY + (ya + A->gy)) * A->nx) * rs;
+                        char *dst = (char *)Bl->field_ptr(s, f) + (((size_t)(zb + Bl->gz) * Bl->NY + (yb + Bl->gy)) * Bl->nx) * rs;
+                        if (backend == TCLB_BACKEND_CUDA) {
+                            if (dy == 0) {   // whole z-plane rows are contiguous in y: one copy per plane
+                                if (y == 0) TCLB_CUDA(cudaMemcpyAsync(dst, src, (size_t)yn * A->nx * rs, cudaMemcpyDefault, (cudaStream_t)A->stream));
+                            } else TCLB_CUDA(cudaMemcpyAsync(dst, src, (size_t)A->nx * rs, cudaMemcpyDefault, (cudaStream_t)A->stream));
+                        } else memcpy(dst, src, (size_t)A->nx * rs);
+                    }
+                }
+        }
+    }
+    if (backend == TCLB_BACKEND_CUDA) sync();
+}
+
+void Domain::run_action(int action, int gmode) {
+    const tclb_action_t &a = model->d->actions[action];
+    int tab0 = lat[local[0]]->cur, tab1 = tab0 ^ 1;
+    for (int s = 0; s < a.n_stages; s++) {
+        int in = s == 0 ? tab0 : tab1;
+        for (int r : local) lat[r]->launch_stage(a.stages[s], in, tab1, gmode);
+        bool need_copy = false;
+        for (int r : local) if (lat[r]->halo_mode == TCLB_HALO_NONE) need_copy = true;
+        if (need_copy) {
+            copy_exchange(tab1);
+            if (exchange_hook) exchange_hook(tab1);
+        }
+    }
+    for (int r : local) lat[r]->cur = tab1;
+}
+void Domain::init() {
+    int a = model->find_action("Init");
+    if (a < 0) fail("model has no Init action");
+    for (int r : local) { lat[r]->iter = 0; lat[r]->reset_iter = 0; }
+    iter = 0;
+    run_action(a, TCLB_GLOBALS_NONE);
+}
+void Domain::iterate(int n, bool globals_on_last, bool globals_every) {
+    int a = model->find_action("Iteration");
+    for (int i = 0; i < n; i++) {
+        bool g = globals_every || (globals_on_last && i == n - 1);
+        if (g) for (int r : local) lat[r]->clear_globals();
+        run_action(a, g ? TCLB_GLOBALS_INTEGRATE : TCLB_GLOBALS_NONE);
+        iter++;
+        for (int r : local) lat[r]->iter = iter;
+    }
+    if (globals_on_last || globals_every) reduce_globals();
+}
+void Domain::reduce_globals() {
+    const int ng = model->d->n_globals;
+    for (int i = 0; i < ng; i++) globals[i] = model->d->globals[i].op == TCLB_OP_MAX ? model->d->globals[i].base : 0.0;
+    for (int r : local) {
+        lat[r]->fetch_globals();
+        for (int i = 0; i < ng; i++) {
+            if (model->d->globals[i].op == TCLB_OP_MAX) globals[i] = std::max(globals[i], lat[r]->globals[i]);
+            else globals[i] += lat[r]->globals[i];
+        }
+    }
+    if (reduce_hook) {
+        const int ns = model->d->sum_globals;
+        reduce_hook(globals.data(), ns, TCLB_OP_SUM);
+        if (ng > ns) reduce_hook(globals.data() + ns, ng - ns, TCLB_OP_MAX);
+    }
+}
+}  // namespace tclb

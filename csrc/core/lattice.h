@@ -1,0 +1,161 @@
+// Lattice: owner of one subdomain's memory and the launcher of its stages.
+//
+// B200-first redesign of the reference's Lattice + LatticeContainer pair
+// (src/Lattice.cu.Rt:87-151 ctor, :466-533 Iteration, :327-389 MPI halo streams, :1279-1315 globals;
+//  src/LatticeContainer.inc.cpp.Rt:144-172 Alloc, :294-342 launches):
+//   * one SoA slab per snapshot with explicit y/z ghost layers instead of 27 margin blocks; the
+//     27-block layout only exists in the checkpoint packer (pri.cpp) for file compatibility;
+//   * no border/interior kernel pair and no host-staged MPI: one fused kernel per stage writes its
+//     outgoing rows directly into the neighbour subdomain's ghost layer (same GPU, a peer GPU over
+//     NVLink, or host memory for the CPU oracle) and publishes a sequence flag;
+//   * launch parameters travel as a __grid_constant__ struct, no constant-memory copy per stage.
+#pragma once
+#include <cstdint>
+#include <functional>
+#include <string>
+#include <vector>
+#include "arena.h"
+#include "model.h"
+#include "zonesettings.h"
+
+namespace tclb {
+
+struct Box {
+    int x0 = 0, y0 = 0, z0 = 0, nx = 0, ny = 0, nz = 0;
+    long long size() const { return (long long)nx * ny * nz; }
+    Box intersect(const Box &o) const;
+    bool empty() const { return nx <= 0 || ny <= 0 || nz <= 0; }
+};
+
+// where the rows that leave through face/edge d=(dy+1)+3(dz+1) have to be written
+struct HaloTarget {
+    int rank = -1;                 // owning rank (may be this one: periodic wrap)
+    void *snap[2] = {nullptr, nullptr};
+    int ny = 0, nz = 0;            // interior extent of the owner
+    unsigned *flag = nullptr;      // owner's flag word that I publish into (its flags_in[opposite(d)])
+};
+
+class Lattice {
+  public:
+    Lattice(Model *model, int backend, int device, int rank, const Box &local, const int total[3]);
+    ~Lattice();
+    Lattice(const Lattice &) = delete;
+
+    Model *model;
+    const int backend, device, rank;
+    Box region;                    // position/extent inside the global lattice
+    int tot[3];
+    int nx, ny, nz, gy, gz, NY, NZ;
+    size_t plane_elems;            // nx*NY*NZ  (elements of one field incl. ghosts)
+    size_t snap_bytes;
+    int cur;                       // snapshot holding the current state
+    int iter, reset_iter;
+    unsigned epoch;                // launches issued so far (halo sequence number)
+    std::vector<double> settings;
+    ZoneSettings zs;
+    std::vector<double> globals;   // last reduced values (local part)
+    int halo_mode;
+    bool sig_enable;
+    HaloTarget halo[TCLB_MAX_NEIGH];
+    void *stream;                  // cudaStream_t
+    int block_x = 0, block_y = 0;
+
+    // ---- memory access ----
+    void *snap_ptr(int i) const { return snap_[i]; }
+    void *flags_ptr() const { return flags_; }
+    unsigned *flags_in() const { return sig_; }            // 9 words written by neighbours
+    void *field_ptr(int snap, int field) const;
+    void flag_overwrite(const uint32_t *flags_local, const Box &local_box);   // box in local coordinates
+    void get_flags(const Box &local_box, uint32_t *out) const;
+    void cuts_overwrite(const uint16_t *cuts_local26);     // [26][nz][ny][nx] or nullptr
+    void copy_field_out(int field, void *dst_native) const;  // interior only, [nz][ny][nx] in real_t
+    void copy_field_in(int field, const void *src_native);
+    void fill_field(int field, double v);
+    void get_quantity(int q, const Box &local_box, void *dst_native, double scale, bool dst_on_device = false);
+    void color(int zplane, float scale, unsigned char *rgba_host_or_dev, bool dst_on_device = false);
+    // ---- settings ----
+    void set_setting(int idx, double v);                   // applies derived-settings chain
+    double get_setting(int idx) const { return settings[idx]; }
+    void set_synthetic_turbulence(const std::vector<tclb_st_mode_t> &modes);
+    // ---- execution ----
+    void launch_stage(int stage, int in_snap, int out_snap, int globals_mode);
+    void clear_globals();
+    void fetch_globals();                                  // device -> this->globals (sync)
+    void sync() const;
+    void upload_zone_table_if_dirty();
+    // raw state (all fields incl. ghosts, current snapshot) for tests / memory dumps
+    void save_raw(const std::string &file) const;
+    void load_raw(const std::string &file);
+    // TCLB-compatible 27-block checkpoint image of the current snapshot (pri.cpp)
+    void save_pri(const std::string &file) const;
+    void load_pri(const std::string &file);
+    size_t pri_bytes() const;
+    bool has_nan(int q, const Box &local_box);
+
+  private:
+    Arena arena_;
+    void *snap_[2];
+    void *flags_;
+    double *globals_dev_;
+    unsigned *sig_;                // [0..8] flags_in, [9] arrival counter
+    void *zone_dev_;
+    size_t zone_dev_bytes_;
+    int zone_stride_;
+    void *cuts_dev_;
+    void *st_dev_;
+    int st_n_;
+    void *scratch_;                // quantity staging
+    size_t scratch_bytes_;
+    void fill_launch(tclb_launch_t &L) const;
+    void *scratch(size_t bytes);
+    void to_host(void *dst, const void *src, size_t bytes) const;
+    void to_dev(void *dst, const void *src, size_t bytes) const;
+};
+
+// Decomposition of the global lattice over ranks: y x z split only, the reference's rule
+// (src/Solver.cpp.Rt:288-370): minimise divz*ny + divy*nz, greedy remainder split, rank = iy + divy*iz.
+struct Decomposition {
+    int nranks = 1, divy = 1, divz = 1;
+    int tot[3] = {0, 0, 0};
+    std::vector<Box> boxes;
+    static Decomposition make(int nx, int ny, int nz, int nranks);
+    int neighbour(int rank, int dy, int dz) const;         // torus
+};
+
+// All subdomains this process owns + wiring between them.
+class Domain {
+  public:
+    Domain(Model *model, int backend, int nx, int ny, int nz, int nranks,
+           const std::vector<int> &local_ranks, const std::vector<int> &devices);
+    ~Domain();
+    Model *model;
+    int backend;
+    Decomposition dec;
+    std::vector<Lattice *> lat;            // indexed by rank; nullptr when remote
+    std::vector<int> local;                // ranks owned here
+    int iter;
+    bool use_direct_halo;                  // fused in-kernel halo (product path) vs copy exchange (baseline)
+    // hooks for multi-process operation
+    std::function<void(int /*epoch*/)> exchange_hook;       // HALO_NONE: external (NCCL/gloo) exchange after every stage
+    std::function<void(double *, int, int)> reduce_hook;    // (values, count, op) across processes
+
+    void connect_local();                  // wire halo targets between local lattices (enables peer access)
+    void set_remote_target(int rank, int d, const HaloTarget &t);
+    void finalize_wiring();                // decide sig_enable per lattice
+    // settings fan-out
+    void set_setting(int idx, double v);
+    void set_zone_setting(int s, int zone, double v);
+    void set_zone_series(int s, int zone, const std::vector<double> &v);
+    void set_zones(int n);
+    // execution
+    void init();
+    void run_action(int action, int globals_mode);
+    void iterate(int n, bool globals_on_last, bool globals_every = false);
+    void copy_exchange(int snap_index);    // baseline: memcpy border rows -> neighbour ghosts (local ranks)
+    void sync();
+    std::vector<double> globals;           // reduced over all ranks
+    void reduce_globals();
+    long long nodes() const { return (long long)dec.tot[0] * dec.tot[1] * dec.tot[2]; }
+};
+
+}  // namespace tclb

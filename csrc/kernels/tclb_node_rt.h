@@ -1,0 +1,100 @@
+// Shared device/host helpers for generated model libraries.
+// Counterpart (new implementation) of the reference's cross-platform shim and reductions
+// (src/cross.h, src/cross.hpp:45-233) reduced to the two targets this framework has:
+// sm_100a device code and a plain C++ host restatement of the same node code (the oracle).
+#pragma once
+#include <cstdint>
+#include <cmath>
+#include <cstring>
+#include <cstdio>
+#include "tclb_model_abi.h"
+
+#if defined(__CUDACC__)
+#define TCLB_HD __host__ __device__ __forceinline__
+#define TCLB_D __device__ __forceinline__
+#else
+#define TCLB_HD inline
+#define TCLB_D inline
+#endif
+#define CudaDeviceFunction TCLB_HD
+
+#ifndef __CUDACC__
+struct float2 { float x, y; };
+struct uchar4 { unsigned char x, y, z, w; };
+#endif
+
+template <class T> struct tclb_vec3 { T x, y, z; };
+
+namespace tclbrt {
+
+template <class T> TCLB_HD T tmax(T a, T b) { return a > b ? a : b; }
+template <class T> TCLB_HD T tmin(T a, T b) { return a < b ? a : b; }
+
+// wrapped x coordinate for an arbitrary (small) offset
+TCLB_HD int wrapx(int x, int dx, int nx) {
+    int v = x + dx;
+    if (v < 0) v += nx;
+    if (v >= nx) v -= nx;
+    return v;
+}
+
+#if defined(__CUDACC__)
+// ---- reductions: warp shuffle -> shared -> one atomic per block (reference K6) -------------
+TCLB_D double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+TCLB_D double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+TCLB_D float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+TCLB_D float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+TCLB_D void atomic_max_double(double *addr, double v) {
+    unsigned long long *p = reinterpret_cast<unsigned long long *>(addr);
+    unsigned long long old = *p, assumed;
+    do {
+        assumed = old;
+        if (__longlong_as_double((long long)assumed) >= v) break;
+        old = atomicCAS(p, assumed, (unsigned long long)__double_as_longlong(v));
+    } while (assumed != old);
+}
+// acquire / release accesses at system scope for the cross-GPU halo flags
+TCLB_D unsigned ld_acquire_sys(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+TCLB_D void st_release_sys(unsigned *p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+#endif
+
+// piecewise colour map used by the headless raster kernel (values in [0,1])
+TCLB_HD void colormap(float v, float mask, unsigned char *rgba) {
+    if (!(v == v)) { rgba[0] = 255; rgba[1] = 0; rgba[2] = 255; rgba[3] = 255; return; }
+    v = v < 0.f ? 0.f : (v > 1.f ? 1.f : v);
+    // blue -> cyan -> green -> yellow -> red
+    float r, g, b;
+    float t = v * 4.f;
+    if (t < 1.f) { r = 0.f; g = t; b = 1.f; }
+    else if (t < 2.f) { r = 0.f; g = 1.f; b = 2.f - t; }
+    else if (t < 3.f) { r = t - 2.f; g = 1.f; b = 0.f; }
+    else { r = 1.f; g = 4.f - t; b = 0.f; }
+    rgba[0] = (unsigned char)(255.f * r * mask);
+    rgba[1] = (unsigned char)(255.f * g * mask);
+    rgba[2] = (unsigned char)(255.f * b * mask);
+    rgba[3] = 255;
+}
+
+}  // namespace tclbrt

@@ -1,0 +1,74 @@
+/* C ABI of the runtime core (libtclb_core.so).  Used by the Python package (ctypes), by the
+ * `tclb` command line driver and by foreign callers.  Every function returns 0 / a valid handle
+ * on success; on failure it returns non-zero / NULL and tclb_last_error() describes why.
+ *
+ * Handles:  tclb_model  - a loaded model library          (reference: one CLB/<model>/ build)
+ *           tclb_domain - all subdomains owned by this process + their halo wiring
+ *                         (reference: Lattice + MPI topology, src/Lattice.cu.Rt, src/Solver.cpp.Rt:288-370)
+ *           tclb_solver - XML case runner (units, geometry, handlers)  (reference: Solver + Handlers, src/main.cpp:173-425)
+ */
+#ifndef TCLB_B200_H
+#define TCLB_B200_H
+#include <stdint.h>
+#include "tclb_model_abi.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tclb_model_h tclb_model_h;
+typedef struct tclb_domain_h tclb_domain_h;
+typedef struct tclb_solver_h tclb_solver_h;
+
+const char *tclb_last_error(void);
+void tclb_log_init(int rank, int level);
+
+/* ---- models (reference src/Lists.cpp.Rt metadata) ---- */
+tclb_model_h *tclb_model_load(const char *path);
+const tclb_model_t *tclb_model_desc(tclb_model_h *);
+
+/* ---- domain / lattice (reference Lattice::*, src/Lattice.h.Rt:39-191) ---- */
+tclb_domain_h *tclb_domain_create(tclb_model_h *, int backend, int nx, int ny, int nz, int nranks,
+                                  const int *local_ranks, int n_local, const int *devices, int n_devices);
+void tclb_domain_destroy(tclb_domain_h *);
+int tclb_domain_decomposition(tclb_domain_h *, int *divy, int *divz, int *boxes6 /* [nranks][6] x0,y0,z0,nx,ny,nz */);
+int tclb_domain_set_halo_mode(tclb_domain_h *, int direct);              /* 1 fused in-kernel (default), 0 copy/NCCL baseline */
+int tclb_domain_set_setting(tclb_domain_h *, const char *name, double value);
+double tclb_domain_get_setting(tclb_domain_h *, const char *name);
+int tclb_domain_set_zone_setting(tclb_domain_h *, const char *name, int zone, double value);
+int tclb_domain_set_zone_series(tclb_domain_h *, const char *name, int zone, const double *v, int n);
+int tclb_domain_set_flags(tclb_domain_h *, int rank, const uint32_t *flags_local);   /* [nz][ny][nx] of that rank */
+int tclb_domain_get_flags(tclb_domain_h *, int rank, uint32_t *flags_local);
+int tclb_domain_set_cuts(tclb_domain_h *, int rank, const uint16_t *cuts26);
+int tclb_domain_init(tclb_domain_h *);                                   /* run action Init */
+int tclb_domain_iterate(tclb_domain_h *, int n, int globals_on_last, int globals_every);
+int tclb_domain_run_action(tclb_domain_h *, const char *action, int globals_mode);
+int tclb_domain_sync(tclb_domain_h *);
+int tclb_domain_iter(tclb_domain_h *);
+int tclb_domain_get_globals(tclb_domain_h *, double *out);              /* n_globals values, reduced over local ranks */
+int tclb_domain_get_field(tclb_domain_h *, int rank, const char *field, void *dst_native);
+int tclb_domain_set_field(tclb_domain_h *, int rank, const char *field, const void *src_native);
+int tclb_domain_get_quantity(tclb_domain_h *, int rank, const char *quantity, const int *box6_local, void *dst_native, double scale);
+int tclb_domain_color(tclb_domain_h *, int rank, int zplane, float scale, unsigned char *rgba);
+int tclb_domain_reset_average(tclb_domain_h *);
+int tclb_domain_set_block(tclb_domain_h *, int bx, int by);
+int tclb_domain_save_pri(tclb_domain_h *, int rank, const char *file);
+int tclb_domain_load_pri(tclb_domain_h *, int rank, const char *file);
+/* raw device views for DLPack/torch coupling: base pointer of the CURRENT snapshot of a rank and its shape
+ * [n_fields][nz+2gz][ny+2gy][nx]; `snap`<0 means current */
+void *tclb_domain_snapshot_ptr(tclb_domain_h *, int rank, int snap, int64_t shape4[4], int *ghost_y, int *ghost_z, int *current);
+void *tclb_domain_flags_ptr(tclb_domain_h *, int rank);
+void *tclb_domain_stream(tclb_domain_h *, int rank);
+/* multi-process wiring (one process per GPU): export my receive side, import a neighbour's */
+int tclb_domain_export_ipc(tclb_domain_h *, int rank, void *handle64, int64_t *off_snap0, int64_t *off_snap1, int64_t *off_flags);
+int tclb_domain_import_peer(tclb_domain_h *, int my_rank, int dir, int peer_rank, const void *handle64,
+                            int64_t off_snap0, int64_t off_snap1, int64_t off_flags, int peer_ny, int peer_nz);
+int tclb_domain_finalize_wiring(tclb_domain_h *);
+/* hooks: external halo exchange (HALO_NONE) and cross-process globals reduction */
+typedef void (*tclb_exchange_fn)(void *user, int snap_index);
+typedef void (*tclb_reduce_fn)(void *user, double *values, int count, int op);
+int tclb_domain_set_hooks(tclb_domain_h *, tclb_exchange_fn ex, tclb_reduce_fn red, void *user);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,193 @@
+"""Build orchestration: generate model sources and compile every native piece for sm_100a.
+
+Replaces the reference's configure + R-template + make pipeline (``makefile``,
+``src/makefile.main.Rt:165-274``, ``src/configure.ac``): `python -m tclb_b200.build d2q9 d3q19`
+produces ``tclb_b200/_lib/libtclb_core.so``, ``tclb_b200/_lib/libtclb_<model>_<float|double>.so``
+and ``bin/tclb``.  Artefacts are built in-tree and keyed by a hash of sources+flags.
+"""
+from __future__ import annotations
+
+import argparse
+import concurrent.futures as cf
+import hashlib
+import json
+import os
+import shutil
+import subprocess
+import sys
+from pathlib import Path
+from typing import Iterable, List, Optional
+
+ROOT = Path(__file__).resolve().parent.parent
+LIBDIR = ROOT / "tclb_b200" / "_lib"
+GENDIR = ROOT / "build" / "gen"
+BINDIR = ROOT / "bin"
+CUDA_HOME = Path(os.environ.get("CUDA_HOME", "/usr/local/cuda"))
+NVCC = str(CUDA_HOME / "bin" / "nvcc")
+ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
+NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-fopenmp,-O2",
+              "-Xptxas", "-v", "-diag-suppress", "177,550"]
+CXX_FLAGS = ["-O2", "-g", "-std=c++17", "-fPIC", "-Wall", "-Wno-unused-function", "-fopenmp"]
+
+
+def _run(cmd: List[str], log: Optional[Path] = None) -> str:
+    p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if log is not None:
+        log.parent.mkdir(parents=True, exist_ok=True)
+        log.write_text(" ".join(cmd) + "\n" + p.stdout)
+    if p.returncode != 0:
+        raise RuntimeError(f"command failed ({p.returncode}): {' '.join(cmd)}\n{p.stdout[-6000:]}")
+    return p.stdout
+
+
+def _hash(paths: Iterable[Path], extra: str = "") -> str:
+    h = hashlib.sha256(extra.encode())
+    for p in sorted(paths):
+        h.update(str(p.relative_to(ROOT)).encode())
+        h.update(p.read_bytes())
+    return h.hexdigest()
+
+
+def _stamp_ok(target: Path, digest: str) -> bool:
+    st = target.with_suffix(target.suffix + ".stamp")
+    return target.exists() and st.exists() and st.read_text() == digest
+
+
+def _stamp(target: Path, digest: str) -> None:
+    target.with_suffix(target.suffix + ".stamp").write_text(digest)
+
+
+CORE_SOURCES = ["csrc/core", "csrc/host", "csrc/handlers", "csrc/io"]
+
+
+def core_sources() -> List[Path]:
+    out: List[Path] = []
+    for d in CORE_SOURCES:
+        out += sorted((ROOT / d).glob("*.cpp"))
+    return out
+
+
+def core_cu_sources() -> List[Path]:
+    out: List[Path] = []
+    for d in CORE_SOURCES + ["csrc/kernels"]:
+        out += sorted((ROOT / d).glob("*.cu"))
+    return out
+
+
+def build_core(force: bool = False, verbose: bool = False) -> Path:
+    LIBDIR.mkdir(parents=True, exist_ok=True)
+    target = LIBDIR / "libtclb_core.so"
+    srcs = core_sources()
+    cus = core_cu_sources()
+    hdrs = [p for d in CORE_SOURCES + ["csrc/kernels", "include"] for p in (ROOT / d).glob("*.h")]
+    digest = _hash(srcs + cus + hdrs, " ".join(CXX_FLAGS + NVCC_FLAGS))
+    if not force and _stamp_ok(target, digest):
+        return target
+    objdir = ROOT / "build" / "core"
+    objdir.mkdir(parents=True, exist_ok=True)
+    incs = ["-I", str(ROOT / "include"), "-I", str(ROOT / "csrc"), "-I", str(ROOT / "csrc/core"), "-I", str(ROOT / "csrc/kernels"),
+            "-I", str(CUDA_HOME / "include")]
+
+    def compile_one(src: Path) -> Path:
+        obj = objdir / (src.parent.name + "_" + src.stem + ".o")
+        d = _hash([src] + hdrs, "obj")
+        if not force and _stamp_ok(obj, d):
+            return obj
+        if src.suffix == ".cu":
+            _run([NVCC] + ARCH_FLAGS + NVCC_FLAGS + incs + ["-c", str(src), "-o", str(obj)], objdir / (obj.name + ".log"))
+        else:
+            _run(["g++"] + CXX_FLAGS + incs + ["-c", str(src), "-o", str(obj)], objdir / (obj.name + ".log"))
+        _stamp(obj, d)
+        return obj
+
+    with cf.ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
+        objs = list(ex.map(compile_one, srcs + cus))
+    _run(["g++", "-shared", "-o", str(target)] + [str(o) for o in objs] +
+         ["-L", str(CUDA_HOME / "lib64"), "-lcudart_static", "-ldl", "-lrt", "-lpthread", "-lgomp", "-lz"])
+    _stamp(target, digest)
+    # command line driver
+    main_src = ROOT / "csrc" / "main.cpp"
+    if main_src.exists():
+        BINDIR.mkdir(exist_ok=True)
+        _run(["g++"] + CXX_FLAGS + incs + [str(main_src), "-o", str(BINDIR / "tclb"), "-L", str(LIBDIR), "-ltclb_core",
+                                          "-Wl,-rpath,$ORIGIN/../tclb_b200/_lib", "-ldl"])
+    if verbose:
+        print(f"built {target}")
+    return target
+
+
+def generate_model(variant: str) -> Path:
+    from .gen.emit import emit_model_source
+    from .models import build_model
+    GENDIR.mkdir(parents=True, exist_ok=True)
+    m = build_model(variant)
+    src = emit_model_source(m, variant)
+    out = GENDIR / f"{variant}.cu"
+    if not out.exists() or out.read_text() != src:
+        out.write_text(src)
+    return out
+
+
+def build_model_lib(variant: str, precision: str = "float", force: bool = False, verbose: bool = False) -> Path:
+    assert precision in ("float", "double")
+    LIBDIR.mkdir(parents=True, exist_ok=True)
+    src = generate_model(variant)
+    target = LIBDIR / f"libtclb_{variant}_{precision}.so"
+    hdrs = [ROOT / "include" / "tclb_model_abi.h", ROOT / "csrc" / "kernels" / "tclb_node_rt.h"]
+    digest = _hash([src] + hdrs, precision + " ".join(NVCC_FLAGS + ARCH_FLAGS))
+    if not force and _stamp_ok(target, digest):
+        return target
+    cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
+    if precision == "double":
+        cmd.append("-DTCLB_DOUBLE")
+    cmd += ["-o", str(target), str(src), "-lgomp"]
+    log = ROOT / "build" / "logs" / f"{variant}_{precision}.ptxas.log"
+    _run(cmd, log)
+    _stamp(target, digest)
+    if verbose:
+        print(f"built {target}")
+    return target
+
+
+DEFAULT_MODELS = ["d2q9", "d2q9_bc", "d3q19", "d3q27_cumulant"]
+
+
+def all_variants() -> List[str]:
+    from .models import base_models, variants
+    out: List[str] = []
+    for b in base_models():
+        out += variants(b)
+    return out
+
+
+def build_all(models: Optional[List[str]] = None, precisions=("float", "double"), force=False, verbose=False, jobs=None) -> None:
+    build_core(force=force, verbose=verbose)
+    models = models or all_variants()
+    tasks = [(m, p) for m in models for p in precisions]
+    with cf.ThreadPoolExecutor(max_workers=jobs or max(1, (os.cpu_count() or 4))) as ex:
+        futs = {ex.submit(build_model_lib, m, p, force, verbose): (m, p) for m, p in tasks}
+        for f in cf.as_completed(futs):
+            f.result()
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(description=__doc__)
+    ap.add_argument("models", nargs="*", help="model variants (default: all registered)")
+    ap.add_argument("--precision", choices=["float", "double", "both"], default="both")
+    ap.add_argument("--force", action="store_true")
+    ap.add_argument("--list", action="store_true")
+    ap.add_argument("--core-only", action="store_true")
+    a = ap.parse_args(argv)
+    if a.list:
+        print("\n".join(all_variants()))
+        return 0
+    if a.core_only:
+        build_core(force=a.force, verbose=True)
+        return 0
+    prec = ("float", "double") if a.precision == "both" else (a.precision,)
+    build_all(a.models or None, prec, a.force, verbose=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
