@@ -9,6 +9,8 @@ from typing import Dict, List, Tuple
 # base model name -> module
 _MODULES: Dict[str, str] = {
     "d2q9": "flow_d2q9",
+    "d3q19": "flow_d3q19",
+    "d3q27_cumulant": "flow_d3q27_cumulant",
 }
 
 

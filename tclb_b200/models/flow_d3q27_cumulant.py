@@ -1,0 +1,319 @@
+"""d3q27 cumulant flow model (options AVG, IB, SMAG).
+
+Model surface of the reference's ``models/flow/d3q27_cumulant`` (Dynamics.R:1-98: 27 densities
+f000..f222 plus same-node field access, settings nu/nubuffer/Velocity/Pressure/Turbulence/
+GalileanCorrection/Force*/Omega[/Smag], Globals Density/Flux/Drag/Lift/Lateral/Mass/*Momentum,
+node types; Dynamics.c.Rt:1-520: raw-moment sweeps, cumulant recursion, relaxation with Galilean
+correction, Zou-He faces, symmetry, interpolated bounce-back on wall cuts, running averages).
+The transforms are generated from the combinatorial recursion in :mod:`tclb_b200.gen.lbmlib`.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from ..gen.lbmlib import (bounce_index, cumulant_from_moments, full_bounce_back, moments_from_cumulant, mrt_eq,
+                          raw_moment_sweeps, symmetry, tensor_names, tensor_velocities, zouhe)
+from ..gen.modeldef import ModelDef
+from ..gen.poly import PV, Poly, PVec, c_assign, to_c
+
+NAME = "d3q27_cumulant"
+OPTIONS = ["AVG", "IB", "SMAG"]
+VARIANTS = [dict(), dict(AVG=True), dict(IB=True), dict(SMAG=True), dict(AVG=True, IB=True), dict(AVG=True, SMAG=True),
+            dict(IB=True, SMAG=True), dict(AVG=True, IB=True, SMAG=True)]
+
+
+def build(options=None) -> ModelDef:
+    opt = dict(AVG=False, IB=False, SMAG=False)
+    opt.update(options or {})
+    m = ModelDef(NAME, opt)
+    U = tensor_velocities(3)
+    fname = tensor_names("f", 3)
+    for i, (n, u) in enumerate(zip(fname, U)):
+        m.AddDensity(name=n, dx=int(u[0]), dy=int(u[1]), dz=int(u[2]), comment=f"density F {i}", group="f")
+    m.AddQuantity(name="P", unit="Pa")
+    m.AddQuantity(name="U", unit="m/s", vector=True)
+    m.AddQuantity(name="Solid", unit="1")
+    m.AddSetting(name="nu", default=0.16666666, comment="Viscosity")
+    m.AddSetting(name="nubuffer", default=0.01, comment="Viscosity in the buffer layer")
+    m.AddSetting(name="Velocity", default="0m/s", comment="Inlet velocity", zonal=True)
+    m.AddSetting(name="Pressure", default="0Pa", comment="Inlet pressure", zonal=True)
+    m.AddSetting(name="Turbulence", comment="Turbulence intensity", zonal=True)
+    m.AddSetting(name="GalileanCorrection", default=1.0, comment="Galilean correction term")
+    m.AddSetting(name="ForceX", default=0, comment="Force force X")
+    m.AddSetting(name="ForceY", default=0, comment="Force force Y")
+    m.AddSetting(name="ForceZ", default=0, comment="Force force Z")
+    m.AddSetting(name="Omega", default=1, comment="relaxation rate for 3rd order cumulants")
+    m.AddGlobal(name="Density", comment="system density", unit="kg/m3")
+    m.AddGlobal(name="Flux", comment="Volume flux", unit="m3/s")
+    m.AddGlobal(name="Drag", comment="Force exerted on body in X-direction", unit="N")
+    m.AddGlobal(name="Lift", comment="Force exerted on body in Z-direction", unit="N")
+    m.AddGlobal(name="Lateral", comment="Force exerted on body in Y-direction", unit="N")
+    m.AddGlobal(name="Mass", comment="Integral of density over the domain", unit="kg")
+    m.AddGlobal(name="XMomentum", comment="Integral of momentum in X", unit="kgm/s")
+    m.AddGlobal(name="YMomentum", comment="Integral of momentum in Y", unit="kgm/s")
+    m.AddGlobal(name="ZMomentum", comment="Integral of momentum in Z", unit="kgm/s")
+    for n in ["Buffer", "WVelocityTurbulent", "NVelocity", "SVelocity", "NPressure", "SPressure"]:
+        m.AddNodeType(name=n, group="BOUNDARY")
+    m.AddNodeType(name="NSymmetry", group="ADDITIONALS")
+    m.AddNodeType(name="SSymmetry", group="ADDITIONALS")
+    m.AddNodeType(name="Body", group="BODY")
+    for n in fname:
+        m.AddField(n, dx=0, dy=0, dz=0)          # same-node access to the pre-streaming value
+    if opt["SMAG"]:
+        m.AddSetting(name="Smag", default=0, comment="Smagorinsky coefficient for SGS modeling")
+    if opt["IB"]:
+        m.AddNodeType(name="IB", group="HO_BOUNDARY")
+    if opt["AVG"]:
+        m.AddQuantity(name="KinE", comment="Turbulent kinetic energy")
+        m.AddQuantity(name="ReStr", comment="Reynolds stress off-diagonal component", vector=True)
+        m.AddQuantity(name="Dissipation", comment="Dissipation e")
+        m.AddQuantity(name="avgU", unit="m/s", vector=True)
+        m.AddQuantity(name="varU", vector=True)
+        m.AddQuantity(name="averageP", unit="Pa")
+        for n in ["avgP", "varUX", "varUY", "varUZ", "varUXUY", "varUXUZ", "varUYUZ", "avgdxu2", "avgdyv2", "avgdzw2"]:
+            m.AddDensity(name=n, dx=0, dy=0, dz=0, average=True)
+        for n in ["avgUX", "avgUY", "avgUZ"]:
+            m.AddDensity(name=n, average=True)
+        m.AddField(name="avgUX", dx=[-1, 1], average=True)
+        m.AddField(name="avgUY", dy=[-1, 1], average=True)
+        m.AddField(name="avgUZ", dz=[1, -1], average=True)
+    for n in ["EPressure", "EVelocity", "Solid", "Wall", "WPressure", "WVelocity"]:
+        m.AddNodeType(name=n, group="BOUNDARY")
+    m.AddNodeType(name="MRT", group="COLLISION")
+    m.code = _physics(m, U, fname, opt)
+    return m
+
+
+def _physics(m: ModelDef, U, fname, opt) -> str:
+    f = PV(fname)
+    dens = m.density_dicts("f")
+    EQ = mrt_eq(U, "rho", ("Jx", "Jy", "Jz"), orthogonal=False)
+    jx, jy, jz = (f @ U[:, k].astype(float) for k in range(3))
+    c = []
+    A = c.append
+    A(f"CudaDeviceFunction real_t getRho() {{\n\treturn {to_c(f.sum())};\n}}")
+    A(f"CudaDeviceFunction real_t getP() {{\n\treturn (({to_c(f.sum())})-1.0)/3.0;\n}}")
+    A("CudaDeviceFunction vector_t getU_() {")
+    A("\treal_t d = getRho();\n\tvector_t u;")
+    A(f"\tu.x = {to_c(jx)};\n\tu.y = {to_c(jy)};\n\tu.z = {to_c(jz)};")
+    A("""	if ((NodeType & NODE_BOUNDARY) == NODE_Wall) {
+		u.x = 0; u.y = 0; u.z = 0;
+	} else {
+		u.x = (u.x + ForceX/2.)/d;
+		u.y = (u.y + ForceY/2.)/d;
+		u.z = (u.z + ForceZ/2.)/d;
+	}
+	return u;
+}
+CudaDeviceFunction vector_t getU() {
+	RunBoundaries();
+	return getU_();
+}
+CudaDeviceFunction real_t getSolid() {
+	return ((NodeType & NODE_BOUNDARY) == NODE_Wall) ? 1 : 0;
+}""")
+    if opt["AVG"]:
+        A("""CudaDeviceFunction real_t getaverageP() { return avgP/average_iter; }
+CudaDeviceFunction real_t getDissipation() {
+	real_t ai = average_iter;
+	real_t gx = avgUX(1,0,0) - avgUX(-1,0,0), gy = avgUY(0,1,0) - avgUY(0,-1,0), gz = avgUZ(0,0,1) - avgUZ(0,0,-1);
+	real_t diss = nu*((avgdxu2/ai) - gx*gx/(4*ai*ai));
+	diss = diss + nu*((avgdyv2/ai) - gy*gy/(4*ai*ai));
+	diss = diss + nu*((avgdzw2/ai) - gz*gz/(4*ai*ai));
+	return diss;
+}
+CudaDeviceFunction vector_t getavgU() {
+	vector_t u;
+	u.x = avgUX(0,0,0)/average_iter;
+	u.y = avgUY(0,0,0)/average_iter;
+	u.z = avgUZ(0,0,0)/average_iter;
+	return u;
+}
+CudaDeviceFunction vector_t getvarU() {
+	vector_t u, a = getavgU();
+	u.x = varUX/average_iter - a.x*a.x;
+	u.y = varUY/average_iter - a.y*a.y;
+	u.z = varUZ/average_iter - a.z*a.z;
+	return u;
+}
+CudaDeviceFunction vector_t getReStr() {
+	vector_t st, a = getavgU();
+	st.x = varUYUZ/average_iter - a.y*a.z;
+	st.y = varUXUZ/average_iter - a.x*a.z;
+	st.z = varUXUY/average_iter - a.x*a.y;
+	return st;
+}
+CudaDeviceFunction real_t getKinE() {
+	vector_t v = getvarU();
+	return 0.5*(v.x + v.y + v.z);
+}""")
+    A("""CudaDeviceFunction float2 Color() {
+	float2 ret;
+	vector_t u = getU();
+	ret.x = sqrt(u.x*u.x + u.y*u.y + u.z*u.z);
+	ret.y = (NodeType == NODE_Solid) ? 0 : 1;
+	return ret;
+}""")
+    A("CudaDeviceFunction void BounceBack() {\n\tvector_t p1, p2;")
+    A(f"\tp1.x = {to_c(jx)};\n\tp1.y = {to_c(jy)};\n\tp1.z = {to_c(jz)};")
+    A(full_bounce_back(dens, "f"))
+    A(f"\tp2.x = {to_c(jx)};\n\tp2.y = {to_c(jy)};\n\tp2.z = {to_c(jz)};")
+    A("""	if ((NodeType & NODE_BODY) == NODE_Body) {
+		AddToDrag(-(p2.x-p1.x));
+		AddToLateral(-(p2.y-p1.y));
+		AddToLift(-(p2.z-p1.z));
+	}
+}""")
+    for nm, direction, sign, kind in [("EVelocity", 1, -1, "velocity"), ("WVelocity", 1, 1, "velocity"),
+                                      ("SVelocity", 2, 1, "velocity"), ("NVelocity", 2, -1, "velocity"),
+                                      ("WPressure", 1, 1, "pressure"), ("SPressure", 2, 1, "pressure"),
+                                      ("NPressure", 2, -1, "pressure"), ("EPressure", 1, -1, "pressure")]:
+        A(f"CudaDeviceFunction void {nm}() {{")
+        A(zouhe(EQ, f, direction, sign, kind))
+        A("}")
+    A("CudaDeviceFunction void NSymmetry() {\n" + symmetry(dens, 2, -1) + "}")
+    A("CudaDeviceFunction void SSymmetry() {\n" + symmetry(dens, 2, 1) + "}")
+    if opt["IB"]:
+        b = bounce_index(U)
+        A("CudaDeviceFunction void InterpolatedBounceBack() {\n\treal_t q;\n\tvector_t F;\n\tF.x = F.y = F.z = 0.0;")
+        qnames = tensor_names("Q", 3)
+        for i in range(1, 27):
+            fo, fb = fname[i], fname[b[i]]
+            A(f"\tq = {qnames[i]};")
+            A("\tif (q != NO_CUT) {")
+            A("\t\treal_t p = ((real_t)q) * (2.0/CUT_MAX);")
+            A(f"\t\treal_t fa = {fo}(0,0,0);")
+            A(f"\t\tif (p > 1.0) {{\n\t\t\t{fb} = fa/p + {fb}(0,0,0)*(p-1)/p;\n\t\t}} else {{\n\t\t\t{fb} = fa*p + {fo}*(1-p);\n\t\t}}")
+            for k, ax in enumerate("xyz"):
+                if U[i, k] != 0:
+                    sgn = "+" if U[i, k] > 0 else "-"
+                    A(f"\t\tF.{ax} = F.{ax} {sgn} ({fb} - fa);")
+            A("\t}")
+        A("""	if ((NodeType & NODE_BODY) == NODE_Body) {
+		AddToDrag(F.x);
+		AddToLateral(F.y);
+		AddToLift(F.z);
+	}
+}""")
+    A("CudaDeviceFunction void RunBoundaries() {")
+    if opt["IB"]:
+        A("\tif ((NodeType & NODE_HO_BOUNDARY) == NODE_IB) InterpolatedBounceBack();")
+    A("""	switch (NodeType & NODE_ADDITIONALS) {
+	case NODE_NSymmetry: NSymmetry(); break;
+	case NODE_SSymmetry: SSymmetry(); break;
+	}
+	switch (NodeType & NODE_BOUNDARY) {
+	case NODE_WVelocityTurbulent: WVelocityTurbulent(); break;
+	case NODE_EPressure: EPressure(); break;
+	case NODE_WPressure: WPressure(); break;
+	case NODE_SPressure: SPressure(); break;
+	case NODE_NPressure: NPressure(); break;
+	case NODE_WVelocity: WVelocity(); break;
+	case NODE_NVelocity: NVelocity(); break;
+	case NODE_SVelocity: SVelocity(); break;
+	case NODE_EVelocity: EVelocity(); break;
+	case NODE_Wall: BounceBack(); break;
+	}
+}
+CudaDeviceFunction void Run() {
+	RunBoundaries();
+	switch (NodeType & NODE_COLLISION) {
+	case NODE_MRT: CollisionMRT(); break;
+	}
+}""")
+    A("CudaDeviceFunction void SetEquilibrum(real_t rho, real_t Jx, real_t Jy, real_t Jz) {")
+    A(c_assign(f, EQ.feq))
+    A("}")
+    A("""CudaDeviceFunction void Init() {
+	vector_t ST = SyntheticTurbulence(X,Y,Z);
+	ST.x = Turbulence*ST.x + Velocity;
+	ST.y = Turbulence*ST.y;
+	ST.z = Turbulence*ST.z;
+	if ((NodeType & NODE_BOUNDARY) == NODE_Wall) SetEquilibrum(1.0, 0, 0, 0);
+	else SetEquilibrum(1.0 + Pressure*3.0, ST.x, ST.y, ST.z);""")
+    A("}")
+    A("""CudaDeviceFunction void WVelocityTurbulent() {
+	vector_t ST = SyntheticTurbulence(X-Time*Velocity,Y,Z);
+	ST.x = Turbulence*ST.x + Velocity;
+	ST.y = Turbulence*ST.y;
+	ST.z = Turbulence*ST.z;""")
+    A(zouhe(EQ, f, 1, 1, "velocity", V="ST.x", V3=["ST.x", "ST.y", "ST.z"]))
+    A("}")
+    # ---- collision ----
+    cum = tensor_names("c", 3)
+    P = np.array([[int(ch) for ch in n[1:]] for n in cum])
+    A("CudaDeviceFunction void CollisionMRT() {")
+    A("""	real_t rho = getRho();
+	vector_t velocity = getU_();
+	AddToDensity( rho );
+	AddToFlux( velocity.x );
+	AddToMass( rho );
+	AddToXMomentum( rho * velocity.x );
+	AddToYMomentum( rho * velocity.y );
+	AddToZMomentum( rho * velocity.z );
+	real_t w0 = 1.0/(3*nu+0.5), w1 = 1.0;
+	if ((NodeType & NODE_BOUNDARY) != 0) w0 = 1.0/(3*nubuffer+0.5);""")
+    A(raw_moment_sweeps("f", forward=True))
+    A("\treal_t " + ", ".join(cum[1:]) + ";")
+    A(cumulant_from_moments("f", "c"))
+    A("""	vector_t u;
+	u.x = c100 + ForceX/(2.*f000);
+	u.y = c010 + ForceY/(2.*f000);
+	u.z = c001 + ForceZ/(2.*f000);""")
+    if opt["SMAG"]:
+        A("""	{
+		real_t tau_0 = (3*nu + 0.5);
+		real_t qq = sqrt((c200-1.0/3)*(c200-1.0/3)+(c020-1.0/3)*(c020-1.0/3)+(c002-1.0/3)*(c002-1.0/3)+2*(c110*c110)+2*(c101*c101)+2*(c011*c011));
+		real_t tau_t = 0.5*(sqrt(tau_0*tau_0 + 18*Smag*Smag*qq) - tau_0);
+		w0 = 1.0/(tau_0 + tau_t);
+		if ((NodeType & NODE_BOUNDARY) != 0) w0 = 1.0/(3*nubuffer+0.5);
+	}""")
+    A("""	real_t dxu, dyv, dzw;
+	dxu = - w0/(2.)*(2*c200 - c020 - c002) - w1/(2.)*(c200 + c020 + c002 - 1.);
+	dyv = dxu + 3.*w0/2.*(c200 - c020);
+	dzw = dxu + 3.*w0/2.*(c200 - c002);""")
+    if opt["AVG"]:
+        A("\tavgdxu2 = avgdxu2 + dxu*dxu;\n\tavgdyv2 = avgdyv2 + dyv*dyv;\n\tavgdzw2 = avgdzw2 + dzw*dzw;")
+    A("""	real_t gcor1 = 3.*(1 - w0/2.)*(u.x*u.x*dxu - u.y*u.y*dyv);
+	real_t gcor2 = 3.*(1 - w0/2.)*(u.x*u.x*dxu - u.z*u.z*dzw);
+	real_t gcor3 = 3.*(1 - w1/2.)*(u.x*u.x*dxu + u.y*u.y*dyv + u.z*u.z*dzw);
+	real_t a, b, cc;
+	a = (1 - w0)*(c200 - c020);
+	b = (1 - w0)*(c200 - c002);
+	cc = w1 + (1 - w1)*(c200 + c020 + c002);
+	a = a - gcor1 * GalileanCorrection;
+	b = b - gcor2 * GalileanCorrection;
+	cc = cc - gcor3 * GalileanCorrection;
+	c100 = c100 + ForceX;
+	c200 = (a + b + cc)/3.;
+	c020 = (cc - 2*a + b)/3.;
+	c002 = (cc - 2*b + a)/3.;
+	c010 = c010 + ForceY;
+	c001 = c001 + ForceZ;
+	c110 = c110 * (1-w0);
+	c011 = c011 * (1-w0);
+	c101 = c101 * (1-w0);""")
+    for n, p in zip(cum, P):
+        if p.sum() == 3:
+            A(f"\t{n} = (1-Omega)*{n};")
+    for n, p in zip(cum, P):
+        if p.sum() > 3:
+            A(f"\t{n} = 0.0;")
+    A(moments_from_cumulant("f", "c"))
+    A(raw_moment_sweeps("f", forward=False))
+    if opt["AVG"]:
+        A("""	{
+		vector_t uu = getU_();
+		avgP = avgP + getP();
+		avgUX = avgUX(0,0,0) + uu.x;
+		avgUY = avgUY(0,0,0) + uu.y;
+		avgUZ = avgUZ(0,0,0) + uu.z;
+		varUX = varUX + uu.x*uu.x;
+		varUY = varUY + uu.y*uu.y;
+		varUZ = varUZ + uu.z*uu.z;
+		varUXUY = varUXUY + uu.x*uu.y;
+		varUXUZ = varUXUZ + uu.x*uu.z;
+		varUYUZ = varUYUZ + uu.y*uu.z;
+	}""")
+    A("}")
+    return "\n".join(c)
