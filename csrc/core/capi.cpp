@@ -185,24 +185,24 @@ void *tclb_domain_snapshot_ptr(tclb_domain_h *h, int rank, int snap, int64_t sha
 void *tclb_domain_flags_ptr(tclb_domain_h *h, int rank) { GUARD_BEGIN return rank_lat(h, rank)->flags_ptr(); GUARD_END_PTR }
 void *tclb_domain_stream(tclb_domain_h *h, int rank) { GUARD_BEGIN return rank_lat(h, rank)->stream; GUARD_END_PTR }
 
-int tclb_domain_export_ipc(tclb_domain_h *h, int rank, void *handle64, int64_t *o0, int64_t *o1, int64_t *of) {
+int tclb_domain_export_ipc(tclb_domain_h *h, int rank, void *handle64, int64_t *offs4) {
     GUARD_BEGIN
     Lattice *l = rank_lat(h, rank);
     if (l->backend != TCLB_BACKEND_CUDA) fail("IPC export needs the CUDA backend");
     TCLB_CUDA(cudaSetDevice(l->device));
-    // the whole subdomain is one allocation: base pointer = snapshot 0 (first arena slot)
+    // the whole subdomain is one allocation, so one handle + four offsets describe it
     cudaIpcMemHandle_t hd;
-    char *base = (char *)l->snap_ptr(0);
+    char *base = (char *)l->arena_base();
     TCLB_CUDA(cudaIpcGetMemHandle(&hd, base));
     static_assert(sizeof(hd) == 64, "cudaIpcMemHandle_t size");
     memcpy(handle64, &hd, 64);
-    *o0 = 0;
-    *o1 = (char *)l->snap_ptr(1) - base;
-    *of = (char *)l->flags_in() - base;
+    offs4[0] = (char *)l->snap_ptr(0) - base;
+    offs4[1] = (char *)l->snap_ptr(1) - base;
+    offs4[2] = (char *)l->flags_in() - base;
+    offs4[3] = (char *)l->gl_ring_ptr() - base;
     GUARD_END_INT
 }
-int tclb_domain_import_peer(tclb_domain_h *h, int my_rank, int dir, int peer_rank, const void *handle64, int64_t o0, int64_t o1,
-                            int64_t of, int pny, int pnz) {
+int tclb_domain_import_peer(tclb_domain_h *h, int my_rank, int peer_rank, const void *handle64, const int64_t *offs4, int pny, int pnz) {
     GUARD_BEGIN
     Lattice *l = rank_lat(h, my_rank);
     TCLB_CUDA(cudaSetDevice(l->device));
@@ -211,15 +211,20 @@ int tclb_domain_import_peer(tclb_domain_h *h, int my_rank, int dir, int peer_ran
     void *base = nullptr;
     TCLB_CUDA(cudaIpcOpenMemHandle(&base, hd, cudaIpcMemLazyEnablePeerAccess));
     h->ipc_opened.push_back(base);
-    HaloTarget t;
-    t.rank = peer_rank;
-    t.snap[0] = (char *)base + o0;
-    t.snap[1] = (char *)base + o1;
-    int dy = dir % 3 - 1, dz = dir / 3 - 1;
-    int opp = (-dy + 1) + 3 * (-dz + 1);
-    t.flag = (unsigned *)((char *)base + of) + opp;
-    t.ny = pny; t.nz = pnz;
-    h->d->set_remote_target(my_rank, dir, t);
+    PeerInfo p;
+    p.valid = true;
+    p.snap[0] = (char *)base + offs4[0];
+    p.snap[1] = (char *)base + offs4[1];
+    p.flags_in = (unsigned *)((char *)base + offs4[2]);
+    p.gl_ring = (double *)((char *)base + offs4[3]);
+    p.ny = pny; p.nz = pnz;
+    h->d->set_peer(my_rank, peer_rank, p);
+    GUARD_END_INT
+}
+int tclb_domain_io_bytes(tclb_domain_h *h, int rank, int64_t *h2d, int64_t *d2h) {
+    GUARD_BEGIN
+    Lattice *l = rank_lat(h, rank);
+    *h2d = (int64_t)l->last_h2d_bytes; *d2h = (int64_t)l->last_d2h_bytes;
     GUARD_END_INT
 }
 int tclb_domain_finalize_wiring(tclb_domain_h *h) { GUARD_BEGIN h->d->finalize_wiring(); GUARD_END_INT }
@@ -232,3 +237,67 @@ int tclb_domain_set_hooks(tclb_domain_h *h, tclb_exchange_fn ex, tclb_reduce_fn 
     else h->d->reduce_hook = nullptr;
     GUARD_END_INT
 }
+
+// ---- units and case runner (host layer) -------------------------------------------------------
+#include "../host/solver.h"
+#include "../host/units.h"
+struct tclb_units_h { UnitEnv env; };
+tclb_units_h *tclb_units_create(void) { return new tclb_units_h(); }
+void tclb_units_destroy(tclb_units_h *u) { delete u; }
+int tclb_units_set(tclb_units_h *u, const char *name, const char *value, const char *gauge) {
+    GUARD_BEGIN
+    u->env.set_unit(name, u->env.read_text(value) / u->env.read_text(gauge));
+    GUARD_END_INT
+}
+int tclb_units_make_gauge(tclb_units_h *u) { GUARD_BEGIN u->env.make_gauge(); GUARD_END_INT }
+int tclb_units_alt(tclb_units_h *u, const char *expr, double *out) { GUARD_BEGIN *out = u->env.alt(std::string(expr)); GUARD_END_INT }
+int tclb_units_si(tclb_units_h *u, const char *expr, double *out, double *exponents9) {
+    GUARD_BEGIN
+    UnitVal v = u->env.read_text(expr);
+    *out = v.val;
+    if (exponents9) for (int i = 0; i < N_BASE_UNITS; i++) exponents9[i] = v.uni[i];
+    GUARD_END_INT
+}
+
+struct tclb_solver_h { Solver *s; tclb_domain_h dom; };
+tclb_solver_h *tclb_solver_create(const char *model, const char *precision, int backend, int nranks, const int *local_ranks, int n_local,
+                                  const int *devices, int n_devices, int direct_halo) {
+    GUARD_BEGIN
+    SolverOptions o;
+    o.model = model;
+    o.precision = precision;
+    o.backend = backend;
+    o.nranks = nranks;
+    if (local_ranks) o.local_ranks.assign(local_ranks, local_ranks + n_local);
+    if (devices) o.devices.assign(devices, devices + n_devices);
+    o.direct_halo = direct_halo != 0;
+    auto *h = new tclb_solver_h();
+    h->s = new Solver(o);
+    h->dom.d = nullptr;
+    return h;
+    GUARD_END_PTR
+}
+void tclb_solver_destroy(tclb_solver_h *h) {
+    if (!h) return;
+    delete h->s;
+    delete h;
+}
+static std::vector<std::string> to_args(const char *const *argv, int argc) {
+    std::vector<std::string> a;
+    for (int i = 0; i < argc; i++) a.push_back(argv[i]);
+    return a;
+}
+int tclb_solver_load_file(tclb_solver_h *h, const char *file, const char *const *xargs, int n) {
+    GUARD_BEGIN h->s->load_case(file, to_args(xargs, n)); h->dom.d = h->s->domain.get(); GUARD_END_INT
+}
+int tclb_solver_load_string(tclb_solver_h *h, const char *xml, const char *name, const char *const *xargs, int n) {
+    GUARD_BEGIN h->s->load_case_string(xml, name, to_args(xargs, n)); h->dom.d = h->s->domain.get(); GUARD_END_INT
+}
+int tclb_solver_run(tclb_solver_h *h) {
+    GUARD_BEGIN
+    if (h->s->run() != 0) fail("case run failed (see log)");
+    GUARD_END_INT
+}
+tclb_domain_h *tclb_solver_domain(tclb_solver_h *h) { return h->dom.d ? &h->dom : nullptr; }
+int tclb_solver_iter(tclb_solver_h *h) { return h->s->iter; }
+const char *tclb_solver_outpath(tclb_solver_h *h) { return h->s->outpath.c_str(); }

@@ -37,11 +37,14 @@ Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &loca
     int sf = arena_.reserve(plane_elems * m->flag_size(), "flags");
     int sg = arena_.reserve(sizeof(double) * std::max(1, m->d->n_globals), "globals");
     int ss = arena_.reserve(sizeof(unsigned) * 64, "halo flags");
+    int sr = arena_.reserve(sizeof(double) * TCLB_GL_RING * TCLB_MAX_RANKS * (std::max(1, m->d->n_globals) + 1), "globals ring");
     arena_.finalize();
+    gl_ring_ = (double *)arena_.ptr(sr);
     snap_[0] = arena_.ptr(s0); snap_[1] = arena_.ptr(s1);
     flags_ = arena_.ptr(sf);
     globals_dev_ = (double *)arena_.ptr(sg);
     sig_ = (unsigned *)arena_.ptr(ss);
+    gl_counter_ = sig_ + 16;
     settings.assign(std::max(1, m->d->n_settings), 0.0);
     globals.assign(std::max(1, m->d->n_globals), 0.0);
     zs.configure(m->d->n_zonesettings, m->d->zone_max + 1);
@@ -50,8 +53,20 @@ Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &loca
         cudaStream_t s;
         TCLB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
         stream = (void *)s;
+        pinned_bytes_ = 1 << 17;
+        TCLB_CUDA(cudaHostAlloc(&pinned_, pinned_bytes_, cudaHostAllocDefault));
     }
     for (int d = 0; d < TCLB_MAX_NEIGH; d++) halo[d] = HaloTarget();
+    clear_globals();
+}
+PeerInfo Lattice::self_info() const {
+    PeerInfo p;
+    p.valid = true;
+    p.snap[0] = snap_[0]; p.snap[1] = snap_[1];
+    p.flags_in = sig_;
+    p.gl_ring = gl_ring_;
+    p.ny = ny; p.nz = nz;
+    return p;
 }
 
 Lattice::~Lattice() {
@@ -62,6 +77,7 @@ Lattice::~Lattice() {
         if (cuts_dev_) cudaFree(cuts_dev_);
         if (st_dev_) cudaFree(st_dev_);
         if (scratch_) cudaFree(scratch_);
+        if (pinned_) cudaFreeHost(pinned_);
     } else {
         free(zone_dev_); free(cuts_dev_); free(st_dev_); free(scratch_);
     }
@@ -229,14 +245,14 @@ void Lattice::upload_zone_table_if_dirty() {
         }
         zone_dev_bytes_ = bytes;
     }
-    if (rs == 4) {
-        std::vector<float> f(tab.begin(), tab.end());
-        if (f.empty()) f.push_back(0.f);
-        to_dev(zone_dev_, f.data(), f.size() * 4);
-    } else {
-        if (tab.empty()) tab.push_back(0.0);
-        to_dev(zone_dev_, tab.data(), tab.size() * 8);
-    }
+    // staged through page-locked host memory so the upload is a true asynchronous DMA
+    if (tab.empty()) tab.push_back(0.0);
+    std::vector<float> f32;
+    const void *src = tab.data();
+    if (rs == 4) { f32.assign(tab.begin(), tab.end()); src = f32.data(); }
+    if (pinned_ && bytes <= pinned_bytes_ / 2) { memcpy(pinned_, src, bytes); src = pinned_; }
+    to_dev(zone_dev_, src, bytes);
+    last_h2d_bytes = bytes;
     zone_stride_ = stride;
     zs.clear_dirty();
 }
@@ -262,7 +278,7 @@ void Lattice::fill_launch(tclb_launch_t &L) const {
     L.block_x = block_x; L.block_y = block_y;
     L.scale = 1.0;
 }
-void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode) {
+void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode, bool publish) {
     upload_zone_table_if_dirty();
     tclb_launch_t L;
     fill_launch(L);
@@ -274,6 +290,17 @@ void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode) {
     L.sig_epoch = epoch;
     L.sig_enable = (sig_enable && halo_mode == TCLB_HALO_DIRECT) ? 1 : 0;
     L.sig_count = sig_ + 9;
+    L.gl_counter = gl_counter_;
+    L.gl_epoch = epoch;
+    L.gl_publish = (gmode != TCLB_GLOBALS_NONE && publish) ? 1 : 0;
+    if (gl_complete) {
+        L.gl_rank = rank; L.gl_nranks = (int)peers.size();
+        for (size_t p = 0; p < peers.size(); p++) L.gl_ring[p] = peers[p].gl_ring;
+    } else {
+        L.gl_rank = 0; L.gl_nranks = 1;
+        L.gl_ring[0] = gl_ring_;
+    }
+    if (L.gl_publish) last_glob_epoch = epoch;
     for (int d = 0; d < TCLB_MAX_NEIGH; d++) {
         if (d == 4) continue;
         L.halo_snap[d] = halo[d].snap[out_snap];
@@ -288,7 +315,7 @@ void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode) {
 }
 void Lattice::clear_globals() {
     std::vector<double> z(model->d->n_globals, 0.0);
-    for (int i = 0; i < model->d->n_globals; i++) z[i] = model->d->globals[i].op == TCLB_OP_MAX ? model->d->globals[i].base : 0.0;
+    for (int i = 0; i < model->d->n_globals; i++) z[i] = model->d->globals[i].op == TCLB_OP_MAX ? -1e300 : 0.0;
     if (backend == TCLB_BACKEND_CUDA) {
         TCLB_CUDA(cudaSetDevice(device));
         TCLB_CUDA(cudaMemcpyAsync(globals_dev_, z.data(), z.size() * sizeof(double), cudaMemcpyHostToDevice, (cudaStream_t)stream));
@@ -296,7 +323,30 @@ void Lattice::clear_globals() {
     } else memcpy(globals_dev_, z.data(), z.size() * sizeof(double));
 }
 void Lattice::fetch_globals() {
-    to_host(globals.data(), globals_dev_, sizeof(double) * model->d->n_globals);
+    // totals of every publishing rank sit in ring slot [epoch % RING]; a stamp equal to the epoch says the
+    // slot is complete.  Ranks run in lock step within a launch or two, so the loop below normally passes once.
+    const int ng = model->d->n_globals, row = ng + 1;
+    const int nr = gl_complete ? (int)peers.size() : 1;
+    const unsigned e = last_glob_epoch;
+    std::vector<double> slot_v;
+    double *slot = pinned_ ? (double *)((char *)pinned_ + pinned_bytes_ / 2) : nullptr;
+    if (!slot || sizeof(double) * (size_t)TCLB_MAX_RANKS * row > pinned_bytes_ / 2) { slot_v.resize((size_t)TCLB_MAX_RANKS * row); slot = slot_v.data(); }
+    const double *src = gl_ring_ + (size_t)(e % TCLB_GL_RING) * TCLB_MAX_RANKS * row;
+    double t0 = walltime();
+    last_d2h_bytes = sizeof(double) * (size_t)nr * row;
+    while (true) {
+        to_host(slot, src, sizeof(double) * (size_t)nr * row);
+        bool ok = true;
+        for (int p = 0; p < nr; p++) if (slot[(size_t)p * row + ng] != (double)e) ok = false;
+        if (ok) break;
+        if (walltime() - t0 > 30.0) fail("rank %d: Globals of launch %u never arrived from every rank (a peer stopped?)", rank, e);
+    }
+    for (int i = 0; i < ng; i++) {
+        const bool mx = model->d->globals[i].op == TCLB_OP_MAX;
+        double v = mx ? model->d->globals[i].base : 0.0;
+        for (int p = 0; p < nr; p++) v = mx ? std::max(v, slot[(size_t)p * row + i]) : v + slot[(size_t)p * row + i];
+        globals[i] = v;
+    }
 }
 void Lattice::get_quantity(int q, const Box &b, void *dst, double scale, bool dst_on_device) {
     upload_zone_table_if_dirty();
@@ -440,48 +490,40 @@ void Domain::connect_local() {
             }
     }
     for (int r : local) {
+        lat[r]->peers.assign(dec.nranks, PeerInfo());
+        for (int q : local) lat[r]->peers[q] = lat[q]->self_info();
+    }
+}
+void Domain::set_peer(int r, int peer, const PeerInfo &p) {
+    if (!lat[r]) fail("set_peer: rank %d is not local", r);
+    lat[r]->peers[peer] = p;
+}
+void Domain::finalize_wiring() {
+    for (int r : local) {
+        Lattice *L = lat[r];
+        bool all_wired = true, concurrent = false, all_peers = true;
+        for (int q = 0; q < dec.nranks; q++) if (!L->peers[q].valid) all_peers = false;
         for (int d = 0; d < TCLB_MAX_NEIGH; d++) {
             if (d == 4) continue;
             int dy = d % 3 - 1, dz = d / 3 - 1;
             int nb = dec.neighbour(r, dy, dz);
-            HaloTarget &t = lat[r]->halo[d];
+            HaloTarget &t = L->halo[d];
+            t = HaloTarget();
             t.rank = nb;
             t.ny = dec.boxes[nb].ny; t.nz = dec.boxes[nb].nz;
-            if (lat[nb]) {
-                t.snap[0] = lat[nb]->snap_ptr(0);
-                t.snap[1] = lat[nb]->snap_ptr(1);
-                t.flag = lat[nb]->flags_in() + opposite(d);
-            }
+            const PeerInfo &p = L->peers[nb];
+            if (p.valid) {
+                t.snap[0] = p.snap[0]; t.snap[1] = p.snap[1];
+                t.flag = p.flags_in + opposite(d);
+            } else all_wired = false;
+            // sequence flags are only needed between kernels that may run concurrently (different devices or
+            // processes); ranks sharing one stream-ordered device do not need them, and the CPU oracle runs
+            // ranks one after another.
+            if (backend == TCLB_BACKEND_CUDA && nb != r && (!lat[nb] || lat[nb]->device != L->device)) concurrent = true;
         }
-    }
-}
-void Domain::set_remote_target(int rank, int d, const HaloTarget &t) {
-    if (!lat[rank]) fail("set_remote_target: rank %d is not local", rank);
-    lat[rank]->halo[d] = t;
-}
-void Domain::finalize_wiring() {
-    for (int r : local) {
-        bool any_remote_dev = false, all_wired = true;
-        for (int d = 0; d < TCLB_MAX_NEIGH; d++) {
-            if (d == 4) continue;
-            HaloTarget &t = lat[r]->halo[d];
-            if (!t.snap[0]) all_wired = false;
-            if (t.rank != r) any_remote_dev = true;
-        }
-        // sequence flags are only needed between kernels that may run concurrently (different
-        // devices / processes); ranks sharing one stream-ordered device do not need them, and the
-        // CPU oracle runs ranks one after another.
-        bool concurrent = false;
-        if (backend == TCLB_BACKEND_CUDA && any_remote_dev) {
-            for (int d = 0; d < TCLB_MAX_NEIGH; d++) {
-                if (d == 4) continue;
-                int nb = lat[r]->halo[d].rank;
-                if (nb == r) continue;
-                if (!lat[nb] || lat[nb]->device != lat[r]->device) concurrent = true;
-            }
-        }
-        lat[r]->sig_enable = concurrent && all_wired;
-        lat[r]->halo_mode = (use_direct_halo && all_wired) ? TCLB_HALO_DIRECT : TCLB_HALO_NONE;
+        L->sig_enable = concurrent && all_wired;
+        L->halo_mode = (use_direct_halo && all_wired) ? TCLB_HALO_DIRECT : TCLB_HALO_NONE;
+        L->gl_complete = all_peers && dec.nranks <= TCLB_MAX_RANKS;
     }
 }
 void Domain::set_setting(int idx, double v) { for (int r : local) lat[r]->set_setting(idx, v); }
@@ -535,7 +577,7 @@ void Domain::run_action(int action, int gmode) {
     int tab0 = lat[local[0]]->cur, tab1 = tab0 ^ 1;
     for (int s = 0; s < a.n_stages; s++) {
         int in = s == 0 ? tab0 : tab1;
-        for (int r : local) lat[r]->launch_stage(a.stages[s], in, tab1, gmode);
+        for (int r : local) lat[r]->launch_stage(a.stages[s], in, tab1, gmode, s == a.n_stages - 1);
         bool need_copy = false;
         for (int r : local) if (lat[r]->halo_mode == TCLB_HALO_NONE) need_copy = true;
         if (need_copy) {
@@ -556,7 +598,6 @@ void Domain::iterate(int n, bool globals_on_last, bool globals_every) {
     int a = model->find_action("Iteration");
     for (int i = 0; i < n; i++) {
         bool g = globals_every || (globals_on_last && i == n - 1);
-        if (g) for (int r : local) lat[r]->clear_globals();
         run_action(a, g ? TCLB_GLOBALS_INTEGRATE : TCLB_GLOBALS_NONE);
         iter++;
         for (int r : local) lat[r]->iter = iter;
@@ -565,14 +606,18 @@ void Domain::iterate(int n, bool globals_on_last, bool globals_every) {
 }
 void Domain::reduce_globals() {
     const int ng = model->d->n_globals;
+    bool complete = true;
+    for (int r : local) { lat[r]->fetch_globals(); if (!lat[r]->gl_complete) complete = false; }
+    if (complete) {            // every rank already holds the totals of all ranks
+        for (int i = 0; i < ng; i++) globals[i] = lat[local[0]]->globals[i];
+        return;
+    }
     for (int i = 0; i < ng; i++) globals[i] = model->d->globals[i].op == TCLB_OP_MAX ? model->d->globals[i].base : 0.0;
-    for (int r : local) {
-        lat[r]->fetch_globals();
+    for (int r : local)
         for (int i = 0; i < ng; i++) {
             if (model->d->globals[i].op == TCLB_OP_MAX) globals[i] = std::max(globals[i], lat[r]->globals[i]);
             else globals[i] += lat[r]->globals[i];
         }
-    }
     if (reduce_hook) {
         const int ns = model->d->sum_globals;
         reduce_hook(globals.data(), ns, TCLB_OP_SUM);

@@ -27,6 +27,16 @@ struct Box {
     bool empty() const { return nx <= 0 || ny <= 0 || nz <= 0; }
 };
 
+// what a rank knows about another rank's memory (own process: plain pointers; other process:
+// pointers obtained from a CUDA IPC mapping of that rank's arena)
+struct PeerInfo {
+    bool valid = false;
+    void *snap[2] = {nullptr, nullptr};
+    unsigned *flags_in = nullptr;  // 9 halo sequence words of that rank
+    double *gl_ring = nullptr;     // its Globals ring
+    int ny = 0, nz = 0;
+};
+
 // where the rows that leave through face/edge d=(dy+1)+3(dz+1) have to be written
 struct HaloTarget {
     int rank = -1;                 // owning rank (may be this one: periodic wrap)
@@ -61,6 +71,13 @@ class Lattice {
     int block_x = 0, block_y = 0;
 
     // ---- memory access ----
+    std::vector<PeerInfo> peers;   // indexed by rank (self included)
+    bool gl_complete = false;      // every rank's ring is mapped: Globals are exchanged in-kernel
+    unsigned last_glob_epoch = 0;
+    size_t last_h2d_bytes = 0, last_d2h_bytes = 0;   // sizes of the last settings upload / Globals read-back
+    PeerInfo self_info() const;
+    double *gl_ring_ptr() const { return gl_ring_; }
+    void *arena_base() const { return arena_.base(); }
     void *snap_ptr(int i) const { return snap_[i]; }
     void *flags_ptr() const { return flags_; }
     unsigned *flags_in() const { return sig_; }            // 9 words written by neighbours
@@ -78,9 +95,9 @@ class Lattice {
     double get_setting(int idx) const { return settings[idx]; }
     void set_synthetic_turbulence(const std::vector<tclb_st_mode_t> &modes);
     // ---- execution ----
-    void launch_stage(int stage, int in_snap, int out_snap, int globals_mode);
+    void launch_stage(int stage, int in_snap, int out_snap, int globals_mode, bool publish_globals = true);
     void clear_globals();
-    void fetch_globals();                                  // device -> this->globals (sync)
+    void fetch_globals();                                  // ring slot of the last publishing launch -> this->globals
     void sync() const;
     void upload_zone_table_if_dirty();
     // raw state (all fields incl. ghosts, current snapshot) for tests / memory dumps
@@ -97,6 +114,8 @@ class Lattice {
     void *snap_[2];
     void *flags_;
     double *globals_dev_;
+    double *gl_ring_;
+    unsigned *gl_counter_;
     unsigned *sig_;                // [0..8] flags_in, [9] arrival counter
     void *zone_dev_;
     size_t zone_dev_bytes_;
@@ -104,6 +123,8 @@ class Lattice {
     void *cuts_dev_;
     void *st_dev_;
     int st_n_;
+    void *pinned_ = nullptr;       // page-locked staging: [0,half) host->device, [half,end) device->host
+    size_t pinned_bytes_ = 0;
     void *scratch_;                // quantity staging
     size_t scratch_bytes_;
     void fill_launch(tclb_launch_t &L) const;
@@ -139,9 +160,9 @@ class Domain {
     std::function<void(int /*epoch*/)> exchange_hook;       // HALO_NONE: external (NCCL/gloo) exchange after every stage
     std::function<void(double *, int, int)> reduce_hook;    // (values, count, op) across processes
 
-    void connect_local();                  // wire halo targets between local lattices (enables peer access)
-    void set_remote_target(int rank, int d, const HaloTarget &t);
-    void finalize_wiring();                // decide sig_enable per lattice
+    void connect_local();                  // publish local lattices to each other (enables peer access)
+    void set_peer(int local_rank, int peer_rank, const PeerInfo &p);
+    void finalize_wiring();                // halo targets from the peer tables; decide sig_enable / Globals mode
     // settings fan-out
     void set_setting(int idx, double v);
     void set_zone_setting(int s, int zone, double v);

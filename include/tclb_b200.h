@@ -59,14 +59,37 @@ void *tclb_domain_snapshot_ptr(tclb_domain_h *, int rank, int snap, int64_t shap
 void *tclb_domain_flags_ptr(tclb_domain_h *, int rank);
 void *tclb_domain_stream(tclb_domain_h *, int rank);
 /* multi-process wiring (one process per GPU): export my receive side, import a neighbour's */
-int tclb_domain_export_ipc(tclb_domain_h *, int rank, void *handle64, int64_t *off_snap0, int64_t *off_snap1, int64_t *off_flags);
-int tclb_domain_import_peer(tclb_domain_h *, int my_rank, int dir, int peer_rank, const void *handle64,
-                            int64_t off_snap0, int64_t off_snap1, int64_t off_flags, int peer_ny, int peer_nz);
+int tclb_domain_export_ipc(tclb_domain_h *, int rank, void *handle64, int64_t offsets4[4] /* snap0, snap1, halo flags, globals ring */);
+int tclb_domain_import_peer(tclb_domain_h *, int my_rank, int peer_rank, const void *handle64, const int64_t offsets4[4],
+                            int peer_ny, int peer_nz);
 int tclb_domain_finalize_wiring(tclb_domain_h *);
+/* bytes moved by the last settings upload (host->device) and the last Globals read-back (device->host) of a rank */
+int tclb_domain_io_bytes(tclb_domain_h *, int rank, int64_t *h2d_bytes, int64_t *d2h_bytes);
 /* hooks: external halo exchange (HALO_NONE) and cross-process globals reduction */
 typedef void (*tclb_exchange_fn)(void *user, int snap_index);
 typedef void (*tclb_reduce_fn)(void *user, double *values, int count, int op);
 int tclb_domain_set_hooks(tclb_domain_h *, tclb_exchange_fn ex, tclb_reduce_fn red, void *user);
+
+
+/* ---- units (reference src/unit.{h,cpp}) ---- */
+typedef struct tclb_units_h tclb_units_h;
+tclb_units_h *tclb_units_create(void);
+void tclb_units_destroy(tclb_units_h *);
+int tclb_units_set(tclb_units_h *, const char *name, const char *value, const char *gauge);
+int tclb_units_make_gauge(tclb_units_h *);
+int tclb_units_alt(tclb_units_h *, const char *expr, double *out);                  /* SI text -> lattice units */
+int tclb_units_si(tclb_units_h *, const char *expr, double *out, double *exponents9); /* SI value + unit exponents */
+
+/* ---- case runner (reference src/main.cpp + Handlers) ---- */
+tclb_solver_h *tclb_solver_create(const char *model, const char *precision, int backend, int nranks, const int *local_ranks,
+                                  int n_local, const int *devices, int n_devices, int direct_halo);
+void tclb_solver_destroy(tclb_solver_h *);
+int tclb_solver_load_file(tclb_solver_h *, const char *case_xml, const char *const *xpath_args, int n_args);
+int tclb_solver_load_string(tclb_solver_h *, const char *xml_text, const char *case_name, const char *const *xpath_args, int n_args);
+int tclb_solver_run(tclb_solver_h *);
+tclb_domain_h *tclb_solver_domain(tclb_solver_h *);     /* borrowed handle, valid while the solver lives */
+int tclb_solver_iter(tclb_solver_h *);
+const char *tclb_solver_outpath(tclb_solver_h *);
 
 #ifdef __cplusplus
 }

@@ -12,8 +12,10 @@
 extern "C" {
 #endif
 
-#define TCLB_ABI_VERSION 3
+#define TCLB_ABI_VERSION 4
 #define TCLB_MAX_NEIGH 9            /* (dy,dz) in {-1,0,1}^2 ; x is never decomposed */
+#define TCLB_MAX_RANKS 16           /* subdomains that exchange Globals through peer memory (one box) */
+#define TCLB_GL_RING 8              /* depth of the Globals publication ring */
 
 enum { TCLB_BACKEND_CPU = 0, TCLB_BACKEND_CUDA = 1 };
 enum { TCLB_GLOBALS_NONE = 0, TCLB_GLOBALS_INTEGRATE = 1, TCLB_GLOBALS_OBJECTIVE = 2 };
@@ -50,7 +52,14 @@ typedef struct {
     void *snap_in, *snap_out;           /* real_t[n_fields][nz+2gz][ny+2gy][nx] */
     const void *flags;                  /* flag_t[nz+2gz][ny+2gy][nx] */
     const void *cuts;                   /* uint16 cut distances [26][...] or NULL */
-    double *globals;                    /* accumulators [n_globals] */
+    double *globals;                    /* local accumulators [n_globals] (kept across the stages of an action) */
+    /* fused Globals exchange: the last block of the last stage stores this rank's totals into slot
+     * [gl_epoch % TCLB_GL_RING][gl_rank] of EVERY rank's ring (peer stores) followed by an epoch stamp,
+     * then resets the accumulators.  Ring layout: double[TCLB_GL_RING][TCLB_MAX_RANKS][n_globals + 1]. */
+    int gl_publish, gl_rank, gl_nranks;
+    double *gl_ring[TCLB_MAX_RANKS];
+    unsigned *gl_counter;
+    unsigned gl_epoch;
     const double *settings;             /* host array [n_settings] */
     const void *zone_table;             /* real_t[zone_len][n_zonesettings][zone_stride] */
     int zone_len, zone_index, zone_stride;

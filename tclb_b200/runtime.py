@@ -151,8 +151,8 @@ def core():
         "tclb_domain_snapshot_ptr": [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)],
         "tclb_domain_flags_ptr": [C.c_void_p, C.c_int],
         "tclb_domain_stream": [C.c_void_p, C.c_int],
-        "tclb_domain_export_ipc": [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)],
-        "tclb_domain_import_peer": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int],
+        "tclb_domain_export_ipc": [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int64)],
+        "tclb_domain_import_peer": [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_int64), C.c_int, C.c_int],
         "tclb_domain_finalize_wiring": [C.c_void_p],
         "tclb_domain_set_hooks": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     }.items():

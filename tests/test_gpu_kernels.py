@@ -1,0 +1,84 @@
+"""GPU tests (run on the B200 box with `-m gpu`): the sm_100a kernels against the CPU restatement of
+the same generated node code, fused halo vs copy baseline on several subdomains, golden karman log."""
+import csv
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from helpers import run_case
+
+pytestmark = pytest.mark.gpu
+
+CASES = [("d2q9", (128, 48, 1)), ("d3q19", (64, 24, 20)), ("d3q27_cumulant", (64, 24, 20))]
+
+
+@pytest.fixture(scope="module", autouse=True)
+def libs(built):
+    from tclb_b200 import build
+    for m, _ in CASES:
+        for p in ("float", "double"):
+            build.build_model_lib(m, p)
+    from tclb_b200.runtime import core
+    core()          # fails loudly if the native library is missing
+
+
+@pytest.mark.parametrize("model,shape", CASES)
+def test_gpu_double_matches_cpu_oracle(model, shape):
+    a = run_case(model, "double", "cpu", shape, 40)
+    b = run_case(model, "double", "cuda", shape, 40)
+    for q in a:
+        if q.startswith("_"):
+            continue
+        assert np.abs(a[q] - b[q]).max() < 1e-12, (model, q, np.abs(a[q] - b[q]).max())   # FMA contraction only
+    for k, v in a["_globals"].items():
+        assert abs(v - b["_globals"][k]) <= 1e-10 * max(1.0, abs(v)), (k, v, b["_globals"][k])
+
+
+@pytest.mark.parametrize("model,shape", CASES)
+def test_gpu_float_matches_fp32_reference(model, shape):
+    a = run_case(model, "double", "cpu", shape, 40)
+    b = run_case(model, "float", "cuda", shape, 40)
+    assert np.abs(a["U"] - b["U"]).max() < 5e-6
+    for k, v in a["_globals"].items():
+        assert abs(v - b["_globals"][k]) <= 2e-4 * max(1.0, abs(v)), (k, v, b["_globals"][k])
+
+
+@pytest.mark.parametrize("model,shape", CASES)
+def test_gpu_virtual_ranks_fused_halo(model, shape):
+    """4 subdomains on one GPU: fused in-kernel ghost stores == memcpy exchange == single subdomain (bitwise)"""
+    a = run_case(model, "float", "cuda", shape, 25, nranks=1)
+    b = run_case(model, "float", "cuda", shape, 25, nranks=4, direct=True)
+    c = run_case(model, "float", "cuda", shape, 25, nranks=4, direct=False)
+    for q in a:
+        if q.startswith("_"):
+            continue
+        assert np.array_equal(a[q], b[q]), (model, q)
+        assert np.array_equal(b[q], c[q]), (model, q)
+
+
+def test_gpu_karman_golden(tclb_bin, tmp_path):
+    from golden_karman import KARMAN_IT1000, KARMAN_XML
+    (tmp_path / "karman.xml").write_text(KARMAN_XML)
+    r = subprocess.run([tclb_bin, "--gpu", "--precision", "double", "d2q9", "karman.xml"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    rows = list(csv.reader(open(tmp_path / "output" / "karman_Log_P00_00000000.csv")))
+    last = dict(zip(rows[0], rows[-1]))
+    for k, v in KARMAN_IT1000.items():
+        assert abs(float(last[k]) - v) <= 1e-8 * abs(v), (k, last[k], v)
+
+
+def test_gpu_smoke_entry():
+    import __graft_entry__ as g
+    g.smoke()
+
+
+def test_multi_gpu_direct_halo_if_available():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("single GPU box")
+    n = min(4, torch.cuda.device_count())
+    a = run_case("d3q27_cumulant", "float", "cuda", (64, 32, 32), 30, nranks=1)
+    b = run_case("d3q27_cumulant", "float", "cuda", (64, 32, 32), 30, nranks=n, devices=list(range(n)))
+    assert np.array_equal(a["U"], b["U"])

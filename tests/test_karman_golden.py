@@ -1,0 +1,100 @@
+"""End-to-end regression against the reference's own golden log (SURVEY.md section 4:
+tests/external/d2q9/karman.test, karman_p2.test, karman_rs.test)."""
+import csv
+import os
+import subprocess
+
+import pytest
+
+from golden_karman import KARMAN_IT1000, KARMAN_XML
+
+
+def _run(tclb_bin, tmp_path, args, xml=KARMAN_XML, name="karman.xml", model="d2q9"):
+    (tmp_path / name).write_text(xml)
+    cmd = [tclb_bin, "--cpu", "--precision", "double"] + args + [model, name]
+    r = subprocess.run(cmd, cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    return r
+
+
+def _log(path):
+    rows = list(csv.reader(open(path)))
+    return rows[0], rows[1:]
+
+
+def _check_it1000(hdr, rows, tol=1e-9):
+    last = dict(zip(hdr, rows[-1]))
+    assert int(last["Iteration"]) == 1000
+    for k, v in KARMAN_IT1000.items():
+        assert abs(float(last[k]) - v) <= tol * abs(v), (k, last[k], v)
+
+
+def test_karman_matches_reference_golden(tclb_bin, tmp_path):
+    from tclb_b200 import build
+    build.build_model_lib("d2q9", "double")
+    _run(tclb_bin, tmp_path, [])
+    hdr, rows = _log(tmp_path / "output" / "karman_Log_P00_00000000.csv")
+    assert len(rows) == 10
+    _check_it1000(hdr, rows)
+    assert (tmp_path / "output" / "karman_config_P00_00000000.xml").exists()
+
+
+def test_karman_full_log_vs_mounted_reference(tclb_bin, tmp_path, reference_dir):
+    from tclb_b200 import build
+    build.build_model_lib("d2q9", "double")
+    _run(tclb_bin, tmp_path, [])
+    hdr, rows = _log(tmp_path / "output" / "karman_Log_P00_00000000.csv")
+    ghdr, grows = _log(os.path.join(reference_dir, "tests/external/d2q9/output/karman_Log_P00_00000000.csv"))
+    assert hdr == ghdr
+    for r, g in zip(rows, grows):
+        for n, a, b in zip(hdr, r, g):
+            if n == "Walltime":
+                continue
+            a, b = float(a), float(b)
+            assert abs(a - b) <= 1e-9 * max(abs(b), 1e-300) or abs(a - b) < 1e-300, (n, a, b)
+
+
+@pytest.mark.parametrize("ranks", [2, 4])
+def test_karman_decomposition_invariance(tclb_bin, tmp_path, ranks):
+    """same goldens with the lattice split over several subdomains (reference karman_p2.test)"""
+    from tclb_b200 import build
+    build.build_model_lib("d2q9", "double")
+    _run(tclb_bin, tmp_path, ["--ranks", str(ranks)])
+    hdr, rows = _log(tmp_path / "output" / "karman_Log_P00_00000000.csv")
+    _check_it1000(hdr, rows)
+
+
+def test_karman_restart(tclb_bin, tmp_path):
+    """run 500 + restart 500 == 1000 (reference karman_rs.test); checkpoint + restart files exist"""
+    from tclb_b200 import build
+    build.build_model_lib("d2q9", "double")
+    xml = KARMAN_XML.replace('<Solve Iterations="1000"><Log Iterations="100"/></Solve>',
+                             '<Solve Iterations="500"><Log Iterations="100"/></Solve><SaveCheckpoint/>')
+    _run(tclb_bin, tmp_path, [], xml=xml)
+    pri = tmp_path / "output" / "karman_checkpoint_00000500_0.pri"
+    rst = tmp_path / "output" / "karman_restart_00000500.xml"
+    assert pri.exists() and rst.exists()
+    text = rst.read_text()
+    assert "LoadBinary" in text
+    # resume: 500 more iterations from the restart file
+    r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", "d2q9", str(rst),
+                        "/CLBConfig/SaveCheckpoint", "delete"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    logs = sorted((tmp_path / "output").glob("karman_restart_00000500_Log_*.csv"))
+    assert logs, os.listdir(tmp_path / "output")
+    hdr, rows = _log(logs[0])
+    last = dict(zip(hdr, rows[-1]))
+    # the resumed run counts iterations from 0, its 500th iteration is the 1000th overall
+    assert int(last["Iteration"]) == 500
+    for k, v in KARMAN_IT1000.items():
+        assert abs(float(last[k]) - v) <= 1e-9 * abs(v), (k, last[k], v)
+
+
+def test_bad_input_fails(tclb_bin, tmp_path):
+    """reference fails.test: malformed cases must fail"""
+    (tmp_path / "bad.xml").write_text("<CLBConfig><Geometry nx='32' ny='8'><NoSuchType><Box/></NoSuchType></Geometry><Model/></CLBConfig>")
+    r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", "d2q9", "bad.xml"], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode != 0
+    (tmp_path / "bad2.xml").write_text("<CLBConfig><Geometry nx='32' ny='8'></CLBConfig>")
+    r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", "d2q9", "bad2.xml"], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode != 0
