@@ -102,6 +102,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (the CPU oracle is not a benchmark target)")
     torch.cuda.set_device(local_rank)
+    from tclb_b200.runtime import core
+    core().tclb_log_init(rank, 6)          # warnings and errors only: stdout carries exactly one JSON line
     shape = tuple(int(v) for v in a.shape.split(",")) if a.shape else SHAPE
     nx, ny, nz = shape
     model = Model(a.model, "float")
@@ -118,9 +120,11 @@ def main():
     if y0 + by_ == ny:
         fl[:, -1, :] = model.flag("Wall")
     dd.set_local_flags(fl)
-    d.set_setting("nu", 0.005)
-    d.set_setting("ForceX", 1e-6)
-    d.set_setting("Velocity", 0.05)
+    known = set(model.settings) | set(model.zonesettings)
+    zonal_input = "Velocity" if "Velocity" in known else ("VelocityX" if "VelocityX" in known else None)
+    for name, val in (("nu", 0.005), ("Viscosity", 0.005), ("ForceX", 1e-6), ("GravitationX", 1e-6), (zonal_input, 0.05)):
+        if name in known:
+            d.set_setting(name, val)
     d.init()
     use_globals = not a.no_globals
     stream = torch.cuda.ExternalStream(d.stream(rank), device=local_rank)
@@ -159,9 +163,10 @@ def main():
     e0.record(stream)
     last = None
     for i in range(e2e_steps):
-        d.set_setting("Velocity", 0.05 + 1e-4 * (i % 7))      # this step's input -> H2D of the zone table
+        if zonal_input:
+            d.set_setting(zonal_input, 0.05 + 1e-4 * (i % 7))  # this step's input -> H2D of the zone table
         d.iterate(1, globals_every=True)                       # fused stream-collide + Globals exchange
-        last = d.globals()["Flux"]                             # this step's result -> D2H of the Globals ring slot
+        last = d.globals()[model.globals[0]]                   # this step's result -> D2H of the Globals ring slot
     e1.record(stream)
     d.sync()
     torch.cuda.synchronize()

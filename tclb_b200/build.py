@@ -111,6 +111,10 @@ def build_core(force: bool = False, verbose: bool = False) -> Path:
         BINDIR.mkdir(exist_ok=True)
         _run(["g++"] + CXX_FLAGS + incs + [str(main_src), "-o", str(BINDIR / "tclb"), "-L", str(LIBDIR), "-ltclb_core",
                                           "-Wl,-rpath,$ORIGIN/../tclb_b200/_lib", "-ldl"])
+    cmp_src = ROOT / "csrc" / "compare.cpp"
+    if cmp_src.exists():
+        _run(["g++"] + CXX_FLAGS + incs + [str(cmp_src), "-o", str(BINDIR / "compare"), "-L", str(LIBDIR), "-ltclb_core",
+                                          "-Wl,-rpath,$ORIGIN/../tclb_b200/_lib", "-ldl"])
     if verbose:
         print(f"built {target}")
     return target
@@ -146,6 +150,29 @@ def build_model_lib(variant: str, precision: str = "float", force: bool = False,
     _stamp(target, digest)
     if verbose:
         print(f"built {target}")
+    return target
+
+
+def build_custom(modeldef, libname: str, precision: str = "double") -> Path:
+    """Compile a ModelDef object under an explicit library name (tests, experiments, user models)."""
+    from .gen.emit import emit_model_source
+    GENDIR.mkdir(parents=True, exist_ok=True)
+    LIBDIR.mkdir(parents=True, exist_ok=True)
+    src = GENDIR / f"{libname}.cu"
+    text = emit_model_source(modeldef, libname)
+    if not src.exists() or src.read_text() != text:
+        src.write_text(text)
+    target = LIBDIR / f"libtclb_{libname}_{precision}.so"
+    hdrs = [ROOT / "include" / "tclb_model_abi.h", ROOT / "csrc" / "kernels" / "tclb_node_rt.h"]
+    digest = _hash([src] + hdrs, precision + " ".join(NVCC_FLAGS + ARCH_FLAGS))
+    if _stamp_ok(target, digest):
+        return target
+    cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
+    if precision == "double":
+        cmd.append("-DTCLB_DOUBLE")
+    cmd += ["-o", str(target), str(src), "-lgomp"]
+    _run(cmd, ROOT / "build" / "logs" / f"{libname}_{precision}.ptxas.log")
+    _stamp(target, digest)
     return target
 
 

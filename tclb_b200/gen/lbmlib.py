@@ -437,3 +437,41 @@ def moments_from_cumulant(mprefix="f", cprefix="c", indent="\t") -> str:
             parts.append(s if coef == 1 else f"( {s} )*{coef}.0")
         lines.append(f"{indent}{_name(mprefix, *al)} = {' + '.join(parts)};")
     return "\n".join(lines) + "\n"
+
+
+# ------------------------------------------------------------------------------------------
+# central-moment sweeps (B200: the cumulant kernel is FP32-issue bound, so the transform is
+# written with the minimum number of dependent FMAs: 6 per triple forward, 7 backward)
+# ------------------------------------------------------------------------------------------
+
+def _triple_names(prefix, ax, j, k):
+    def nm(d):
+        t = [0, 0, 0]
+        others = [a for a in range(3) if a != ax]
+        t[ax] = d
+        t[others[0]] = j
+        t[others[1]] = k
+        return _name(prefix, *t)
+    return nm(0), nm(1), nm(2)
+
+
+def central_moment_forward(prefix: str, u: Sequence[str], indent="\t") -> str:
+    """populations (digit 0,1,2 = velocity 0,+1,-1) -> central moments about u (digit = power), in place."""
+    out = [f"{indent}real_t cm_a, cm_b;"]
+    for ax in range(3):
+        for j, k in product(range(3), repeat=2):
+            z, p, m = _triple_names(prefix, ax, j, k)
+            out.append(f"{indent}cm_a = {p} + {m}; cm_b = {p} - {m}; {z} = {z} + cm_a; "
+                       f"{p} = cm_b - {u[ax]}*{z}; {m} = cm_a - {u[ax]}*(cm_b + {p});")
+    return "\n".join(out) + "\n"
+
+
+def central_moment_backward(prefix: str, u: Sequence[str], indent="\t") -> str:
+    """central moments about u -> populations, in place (inverse of central_moment_forward)."""
+    out = [f"{indent}real_t cr_1, cr_2;"]
+    for ax in range(3):
+        for j, k in product(range(3), repeat=2):
+            z, p, m = _triple_names(prefix, ax, j, k)
+            out.append(f"{indent}cr_1 = {p} + {u[ax]}*{z}; cr_2 = {m} + {u[ax]}*({p} + cr_1); {z} = {z} - cr_2; "
+                       f"{p} = (cr_2 + cr_1)*0.5; {m} = cr_2 - {p};")
+    return "\n".join(out) + "\n"

@@ -155,7 +155,8 @@ class DistDomain:
         lib = self.domain.lib
         lib.tclb_domain_io_bytes.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         # prime both paths once so the sizes are known
-        self.domain.set_setting("Velocity" if "Velocity" in self.model.zonesettings else self.model.zonesettings[0], 0.05)
+        zs = self.model.zonesettings
+        self.domain.set_setting("Velocity" if "Velocity" in zs else ("VelocityX" if "VelocityX" in zs else zs[0]), 0.05)
         self.domain.iterate(1, globals_every=True)
         self.domain.globals()
         a, b = C.c_int64(), C.c_int64()

@@ -41,8 +41,10 @@ def test_gpu_float_matches_fp32_reference(model, shape):
     a = run_case(model, "double", "cpu", shape, 40)
     b = run_case(model, "float", "cuda", shape, 40)
     assert np.abs(a["U"] - b["U"]).max() < 5e-6
+    n = float(np.prod(shape))
     for k, v in a["_globals"].items():
-        assert abs(v - b["_globals"][k]) <= 2e-4 * max(1.0, abs(v)), (k, v, b["_globals"][k])
+        # fp32 node values carry ~1e-7 relative rounding; a sum over n nodes of O(1) populations may drift by n*1e-7
+        assert abs(v - b["_globals"][k]) <= 2e-4 * max(1.0, abs(v)) + 2e-7 * n, (k, v, b["_globals"][k])
 
 
 @pytest.mark.parametrize("model,shape", CASES)
