@@ -22,7 +22,7 @@ Box Box::intersect(const Box &o) const {
 }
 
 // ------------------------------------------------------------------------------------------
-Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &local, const int total[3])
+Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &local, const int total[3], void *shared_stream)
     : model(m), backend(backend_), device(device_), rank(rank_), region(local), cur(0), iter(0), reset_iter(0), epoch(0),
       halo_mode(TCLB_HALO_DIRECT), sig_enable(false), stream(nullptr), arena_(backend_, device_), zone_dev_(nullptr),
       zone_dev_bytes_(0), zone_stride_(1), cuts_dev_(nullptr), st_dev_(nullptr), st_n_(0), scratch_(nullptr), scratch_bytes_(0) {
@@ -35,7 +35,7 @@ Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &loca
     int s0 = arena_.reserve(snap_bytes, "snapshot0");
     int s1 = arena_.reserve(snap_bytes, "snapshot1");
     int sf = arena_.reserve(plane_elems * m->flag_size(), "flags");
-    int sg = arena_.reserve(sizeof(double) * std::max(1, m->d->n_globals), "globals");
+    int sg = arena_.reserve(sizeof(double) * TCLB_GL_SLOTS * std::max(1, m->d->n_globals), "globals");
     int ss = arena_.reserve(sizeof(unsigned) * 64, "halo flags");
     int sr = arena_.reserve(sizeof(double) * TCLB_GL_RING * TCLB_MAX_RANKS * (std::max(1, m->d->n_globals) + 1), "globals ring");
     arena_.finalize();
@@ -50,9 +50,16 @@ Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &loca
     zs.configure(m->d->n_zonesettings, m->d->zone_max + 1);
     if (backend == TCLB_BACKEND_CUDA) {
         TCLB_CUDA(cudaSetDevice(device));
-        cudaStream_t s;
-        TCLB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-        stream = (void *)s;
+        // subdomains that share a device share ONE stream: their launches are then ordered, which is what
+        // makes several ranks per GPU correct without halo flags (and flags between co-resident kernels on one
+        // GPU could dead-lock: nothing guarantees that two launches run at the same time)
+        if (shared_stream) { stream = shared_stream; owns_stream_ = false; }
+        else {
+            cudaStream_t s;
+            TCLB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+            stream = (void *)s;
+            owns_stream_ = true;
+        }
         pinned_bytes_ = 1 << 17;
         TCLB_CUDA(cudaHostAlloc(&pinned_, pinned_bytes_, cudaHostAllocDefault));
     }
@@ -72,7 +79,7 @@ PeerInfo Lattice::self_info() const {
 Lattice::~Lattice() {
     if (backend == TCLB_BACKEND_CUDA) {
         cudaSetDevice(device);
-        if (stream) cudaStreamDestroy((cudaStream_t)stream);
+        if (stream && owns_stream_) cudaStreamDestroy((cudaStream_t)stream);
         if (zone_dev_) cudaFree(zone_dev_);
         if (cuts_dev_) cudaFree(cuts_dev_);
         if (st_dev_) cudaFree(st_dev_);
@@ -314,13 +321,11 @@ void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode, bool
     if (model->d->run_stage(stage, &L) != 0) fail("stage %s failed: %s", model->d->stages[stage].name, model->d->last_error());
 }
 void Lattice::clear_globals() {
-    std::vector<double> z(model->d->n_globals, 0.0);
-    for (int i = 0; i < model->d->n_globals; i++) z[i] = model->d->globals[i].op == TCLB_OP_MAX ? -1e300 : 0.0;
-    if (backend == TCLB_BACKEND_CUDA) {
-        TCLB_CUDA(cudaSetDevice(device));
-        TCLB_CUDA(cudaMemcpyAsync(globals_dev_, z.data(), z.size() * sizeof(double), cudaMemcpyHostToDevice, (cudaStream_t)stream));
-        TCLB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));   // z is a stack-local staging buffer
-    } else memcpy(globals_dev_, z.data(), z.size() * sizeof(double));
+    const int ng = model->d->n_globals;
+    std::vector<double> z((size_t)TCLB_GL_SLOTS * std::max(1, ng), 0.0);
+    for (int s = 0; s < TCLB_GL_SLOTS; s++)
+        for (int i = 0; i < ng; i++) z[(size_t)s * ng + i] = model->d->globals[i].op == TCLB_OP_MAX ? -1e300 : 0.0;
+    to_dev(globals_dev_, z.data(), z.size() * sizeof(double));
 }
 void Lattice::fetch_globals() {
     // totals of every publishing rank sit in ring slot [epoch % RING]; a stamp equal to the epoch says the
@@ -458,7 +463,9 @@ Domain::Domain(Model *m, int backend_, int nx, int ny, int nz, int nranks, const
     for (size_t i = 0; i < local.size(); i++) {
         int r = local[i];
         int dev = devices.empty() ? 0 : devices[i % devices.size()];
-        lat[r] = new Lattice(m, backend, dev, r, dec.boxes[r], dec.tot);
+        void *shared = nullptr;
+        for (size_t k = 0; k < i; k++) if (lat[local[k]]->device == dev) shared = lat[local[k]]->stream;
+        lat[r] = new Lattice(m, backend, dev, r, dec.boxes[r], dec.tot, shared);
     }
     globals.assign(std::max(1, m->d->n_globals), 0.0);
     // defaults of the settings are applied by the Solver (needs the unit system)
@@ -466,7 +473,8 @@ Domain::Domain(Model *m, int backend_, int nx, int ny, int nz, int nranks, const
     finalize_wiring();
 }
 Domain::~Domain() {
-    for (auto *l : lat) delete l;
+    try { sync(); } catch (...) {}
+    for (size_t i = lat.size(); i-- > 0;) delete lat[i];     // stream owners (first on a device) go last
 }
 static int opposite(int d) {
     int dy = d % 3 - 1, dz = d / 3 - 1;

@@ -47,7 +47,7 @@ struct HaloTarget {
 
 class Lattice {
   public:
-    Lattice(Model *model, int backend, int device, int rank, const Box &local, const int total[3]);
+    Lattice(Model *model, int backend, int device, int rank, const Box &local, const int total[3], void *shared_stream = nullptr);
     ~Lattice();
     Lattice(const Lattice &) = delete;
 
@@ -123,6 +123,7 @@ class Lattice {
     void *cuts_dev_;
     void *st_dev_;
     int st_n_;
+    bool owns_stream_ = false;
     void *pinned_ = nullptr;       // page-locked staging: [0,half) host->device, [half,end) device->host
     size_t pinned_bytes_ = 0;
     void *scratch_;                // quantity staging

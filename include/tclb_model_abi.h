@@ -12,10 +12,11 @@
 extern "C" {
 #endif
 
-#define TCLB_ABI_VERSION 4
+#define TCLB_ABI_VERSION 5
 #define TCLB_MAX_NEIGH 9            /* (dy,dz) in {-1,0,1}^2 ; x is never decomposed */
 #define TCLB_MAX_RANKS 16           /* subdomains that exchange Globals through peer memory (one box) */
 #define TCLB_GL_RING 8              /* depth of the Globals publication ring */
+#define TCLB_GL_SLOTS 128           /* replicas of the local accumulators (spreads same-address atomics over L2 slices) */
 
 enum { TCLB_BACKEND_CPU = 0, TCLB_BACKEND_CUDA = 1 };
 enum { TCLB_GLOBALS_NONE = 0, TCLB_GLOBALS_INTEGRATE = 1, TCLB_GLOBALS_OBJECTIVE = 2 };
@@ -52,7 +53,7 @@ typedef struct {
     void *snap_in, *snap_out;           /* real_t[n_fields][nz+2gz][ny+2gy][nx] */
     const void *flags;                  /* flag_t[nz+2gz][ny+2gy][nx] */
     const void *cuts;                   /* uint16 cut distances [26][...] or NULL */
-    double *globals;                    /* local accumulators [n_globals] (kept across the stages of an action) */
+    double *globals;                    /* local accumulators [TCLB_GL_SLOTS][n_globals] (kept across the stages of an action) */
     /* fused Globals exchange: the last block of the last stage stores this rank's totals into slot
      * [gl_epoch % TCLB_GL_RING][gl_rank] of EVERY rank's ring (peer stores) followed by an epoch stamp,
      * then resets the accumulators.  Ring layout: double[TCLB_GL_RING][TCLB_MAX_RANKS][n_globals + 1]. */

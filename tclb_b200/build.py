@@ -153,7 +153,7 @@ def build_model_lib(variant: str, precision: str = "float", force: bool = False,
     return target
 
 
-def build_custom(modeldef, libname: str, precision: str = "double") -> Path:
+def build_custom(modeldef, libname: str, precision: str = "double", extra_flags=()) -> Path:
     """Compile a ModelDef object under an explicit library name (tests, experiments, user models)."""
     from .gen.emit import emit_model_source
     GENDIR.mkdir(parents=True, exist_ok=True)
@@ -164,10 +164,10 @@ def build_custom(modeldef, libname: str, precision: str = "double") -> Path:
         src.write_text(text)
     target = LIBDIR / f"libtclb_{libname}_{precision}.so"
     hdrs = [ROOT / "include" / "tclb_model_abi.h", ROOT / "csrc" / "kernels" / "tclb_node_rt.h"]
-    digest = _hash([src] + hdrs, precision + " ".join(NVCC_FLAGS + ARCH_FLAGS))
+    digest = _hash([src] + hdrs, precision + " ".join(NVCC_FLAGS + ARCH_FLAGS + list(extra_flags)))
     if _stamp_ok(target, digest):
         return target
-    cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
+    cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + list(extra_flags) + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
     if precision == "double":
         cmd.append("-DTCLB_DOUBLE")
     cmd += ["-o", str(target), str(src), "-lgomp"]

@@ -475,3 +475,32 @@ def central_moment_backward(prefix: str, u: Sequence[str], indent="\t") -> str:
             out.append(f"{indent}cr_1 = {p} + {u[ax]}*{z}; cr_2 = {m} + {u[ax]}*({p} + cr_1); {z} = {z} - cr_2; "
                        f"{p} = (cr_2 + cr_1)*0.5; {m} = cr_2 - {p};")
     return "\n".join(out) + "\n"
+
+
+def central_moment_forward_shared(prefix: str, rho: str, j: Sequence[str], u: Sequence[str], irho: str, indent="\t") -> str:
+    """Forward central-moment transform that also produces density and momentum from the partial sums of
+    its own first (x) pass: rho and J cost 8+8+5+5 additions instead of 26+3*17."""
+    out = [f"{indent}real_t cm_a, cm_b;"]
+    ax = 0
+    for jj, k in product(range(3), repeat=2):
+        z, p, m = _triple_names(prefix, ax, jj, k)
+        out.append(f"{indent}cm_a = {p} + {m}; {p} = {p} - {m}; {m} = cm_a; {z} = {z} + cm_a;")
+    def nm(a, b, c):
+        return _name(prefix, a, b, c)
+    zs = [nm(0, b, c) for c in range(3) for b in range(3)]
+    out.append(f"{indent}real_t {rho} = ((({zs[0]} + {zs[1]}) + ({zs[2]} + {zs[3]})) + (({zs[4]} + {zs[5]}) + ({zs[6]} + {zs[7]}))) + {zs[8]};")
+    bs = [nm(1, b, c) for c in range(3) for b in range(3)]
+    out.append(f"{indent}real_t {j[0]} = ((({bs[0]} + {bs[1]}) + ({bs[2]} + {bs[3]})) + (({bs[4]} + {bs[5]}) + ({bs[6]} + {bs[7]}))) + {bs[8]};")
+    out.append(f"{indent}real_t {j[1]} = (({nm(0,1,0)} - {nm(0,2,0)}) + ({nm(0,1,1)} - {nm(0,2,1)})) + ({nm(0,1,2)} - {nm(0,2,2)});")
+    out.append(f"{indent}real_t {j[2]} = (({nm(0,0,1)} - {nm(0,0,2)}) + ({nm(0,1,1)} - {nm(0,1,2)})) + ({nm(0,2,1)} - {nm(0,2,2)});")
+    out.append(f"{indent}real_t {irho} = 1.0/{rho};")
+    out.append(f"{indent}{u[0]} = {j[0]}*{irho}; {u[1]} = {j[1]}*{irho}; {u[2]} = {j[2]}*{irho};")
+    for jj, k in product(range(3), repeat=2):
+        z, p, m = _triple_names(prefix, ax, jj, k)
+        out.append(f"{indent}cm_b = {p}; {p} = cm_b - {u[0]}*{z}; {m} = {m} - {u[0]}*(cm_b + {p});")
+    for ax in (1, 2):
+        for jj, k in product(range(3), repeat=2):
+            z, p, m = _triple_names(prefix, ax, jj, k)
+            out.append(f"{indent}cm_a = {p} + {m}; cm_b = {p} - {m}; {z} = {z} + cm_a; "
+                       f"{p} = cm_b - {u[ax]}*{z}; {m} = cm_a - {u[ax]}*(cm_b + {p});")
+    return "\n".join(out) + "\n"

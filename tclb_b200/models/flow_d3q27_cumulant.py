@@ -11,7 +11,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from ..gen.lbmlib import (bounce_index, central_moment_backward, central_moment_forward, cumulant_from_moments, full_bounce_back, moments_from_cumulant, mrt_eq,
+from ..gen.lbmlib import (bounce_index, central_moment_backward, central_moment_forward, central_moment_forward_shared, cumulant_from_moments, full_bounce_back, moments_from_cumulant, mrt_eq,
                           raw_moment_sweeps, symmetry, tensor_names, tensor_velocities, zouhe)
 from ..gen.modeldef import ModelDef
 from ..gen.poly import PV, Poly, PVec, c_assign, to_c
@@ -343,11 +343,21 @@ def _collision_central(A, opt, jx="0", jy="0", jz="0"):
     follow in closed form from the relaxed 2nd/3rd-order ones - the pre-collision high-order cumulants are never
     formed.  The first-order shift by the body force enters as the velocity of the backward sweep."""
     A("CudaDeviceFunction void CollisionMRT() {")
-    A(_COLLISION_PROLOGUE)
-    A("	real_t irho = 1.0/rho;")
     A("	vector_t u0;      // momentum/density without the half-force shift: the first raw cumulant")
-    A(f"	u0.x = ({jx})*irho;\n	u0.y = ({jy})*irho;\n	u0.z = ({jz})*irho;")
-    A(central_moment_forward("f", ["u0.x", "u0.y", "u0.z"]))
+    A(central_moment_forward_shared("f", "rho", ["jx", "jy", "jz"], ["u0.x", "u0.y", "u0.z"], "irho"))
+    A("""	{
+		vector_t velocity;      // what the quantity U reports: half-force shifted, zero on walls
+		if ((NodeType & NODE_BOUNDARY) == NODE_Wall) { velocity.x = 0; velocity.y = 0; velocity.z = 0; }
+		else { velocity.x = u0.x + ForceX*0.5*irho; velocity.y = u0.y + ForceY*0.5*irho; velocity.z = u0.z + ForceZ*0.5*irho; }
+		AddToDensity( rho );
+		AddToFlux( velocity.x );
+		AddToMass( rho );
+		AddToXMomentum( rho * velocity.x );
+		AddToYMomentum( rho * velocity.y );
+		AddToZMomentum( rho * velocity.z );
+	}
+	real_t w0 = 1.0/(3*nu+0.5), w1 = 1.0;
+	if ((NodeType & NODE_BOUNDARY) != 0) w0 = 1.0/(3*nubuffer+0.5);""")
     second = ["200", "020", "002", "110", "101", "011"]
     third = ["210", "201", "120", "021", "102", "012", "111", "300"]
     third = [t for t in third if max(int(ch) for ch in t) <= 2]
