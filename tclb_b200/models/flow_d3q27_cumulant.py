@@ -84,6 +84,8 @@ def build(options=None, collision="central") -> ModelDef:
         m.AddNodeType(name=n, group="BOUNDARY")
     m.AddNodeType(name="MRT", group="COLLISION")
     m.code = _physics(m, U, fname, opt, collision)
+    # measured on B200 (profiles/): 64 registers/thread -> 8 blocks of 128 threads per SM is the fastest fp32 build
+    m.tuning = dict(min_blocks_float=8, min_blocks_double=3)
     return m
 
 
