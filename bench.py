@@ -95,6 +95,11 @@ def main():
     from tclb_b200.parallel.dist import DistDomain
     from tclb_b200.runtime import Model
 
+    # stdout must carry exactly one JSON line: libraries (NCCL prints its version banner there) write to fd 1,
+    # so fd 1 is pointed at stderr until the result is ready
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -199,8 +204,14 @@ def main():
                          "hbm_gbs_measured": hbm, "fraction_of_measured_hbm": round(value * 1e6 * bytes_per_update / 1e9 / a.gpus / hbm, 3)},
             "globals_sample": {k: g[k] for k in list(g)[:4]}, "last_e2e_flux": last,
         }
-        print(json.dumps(out))
+        result_line = json.dumps(out)
+    else:
+        result_line = None
     dd.close()
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
+    if result_line is not None:
+        os.write(1, (result_line + "\n").encode())
     return 0
 
 
