@@ -1,5 +1,6 @@
 #include "lattice.h"
 #include "common.h"
+#include "tclb_b200.h"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -385,6 +386,17 @@ void Lattice::color(int zplane, float scale, unsigned char *rgba, bool dst_on_de
 bool Lattice::has_nan(int q, const Box &b) {
     const int nc = model->d->quantities[q].vector ? 3 : 1;
     size_t n = (size_t)b.size() * nc;
+    if (backend == TCLB_BACKEND_CUDA) {
+        // quantity -> device staging -> device scan: only 24 bytes come back (reference copies the whole field)
+        const size_t bytes = n * model->real_size(), off = (bytes + 255) & ~(size_t)255;
+        char *buf = (char *)scratch(off + 64);
+        get_quantity(q, b, buf, 1.0, true);
+        if (tclb_scan_array(buf, (long long)n, model->real_size(), stream, (double *)(buf + off)) != 0)
+            fail("device scan failed: %s", tclb_scan_last_error());
+        double r[3];
+        to_host(r, buf + off, sizeof(r));
+        return r[0] > 0;
+    }
     std::vector<char> buf(n * model->real_size());
     get_quantity(q, b, buf.data(), 1.0);
     if (model->real_size() == 4) { const float *p = (const float *)buf.data(); for (size_t i = 0; i < n; i++) if (!(p[i] == p[i])) return true; }

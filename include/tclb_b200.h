@@ -71,6 +71,13 @@ typedef void (*tclb_reduce_fn)(void *user, double *values, int count, int op);
 int tclb_domain_set_hooks(tclb_domain_h *, tclb_exchange_fn ex, tclb_reduce_fn red, void *user);
 
 
+/* ---- device scan (reference: host loop in src/Handlers/cbFailcheck.cpp:66-72) ----
+ * result3_dev[0..2] (DEVICE memory) = number of NaNs, minimum and maximum of the non-NaN values of the device array
+ * dev_ptr[0..n) of floats (real_size 4) or doubles (8).  Asynchronous on `stream` (cudaStream_t); the current device
+ * must be the one that owns dev_ptr.  Uses a cudaMalloc'ed scratch buffer that grows with n (kept per device). */
+int tclb_scan_array(const void *dev_ptr, long long n, int real_size, void *stream, double *result3_dev);
+const char *tclb_scan_last_error(void);
+
 /* ---- units (reference src/unit.{h,cpp}) ---- */
 typedef struct tclb_units_h tclb_units_h;
 tclb_units_h *tclb_units_create(void);

@@ -84,3 +84,44 @@ def test_multi_gpu_direct_halo_if_available():
     a = run_case("d3q27_cumulant", "float", "cuda", (64, 32, 32), 30, nranks=1)
     b = run_case("d3q27_cumulant", "float", "cuda", (64, 32, 32), 30, nranks=n, devices=list(range(n)))
     assert np.array_equal(a["U"], b["U"])
+
+
+def _scan(lib, t):
+    import ctypes as C
+    import torch
+    out = torch.zeros(3, dtype=torch.float64, device=t.device)
+    lib.tclb_scan_array.argtypes = [C.c_void_p, C.c_longlong, C.c_int, C.c_void_p, C.c_void_p]
+    lib.tclb_scan_last_error.restype = C.c_char_p
+    rc = lib.tclb_scan_array(t.data_ptr(), t.numel(), t.element_size(), None, out.data_ptr())
+    assert rc == 0, lib.tclb_scan_last_error()
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+@pytest.mark.parametrize("n,dtype", [(1, "float32"), (4097, "float32"), (1 << 20, "float64"), (3_000_001, "float32")])
+def test_device_scan_matches_numpy(n, dtype):
+    import torch
+    from tclb_b200.runtime import core
+    lib = core()
+    rng = np.random.default_rng(n)
+    a = rng.standard_normal(n).astype(dtype)
+    k = min(n, 5)
+    idx = rng.choice(n, size=k, replace=False) if n > 5 else np.array([], dtype=int)
+    a[idx] = np.nan
+    t = torch.from_numpy(a).cuda()
+    for _ in range(2):
+        r = _scan(lib, t)
+        fin = a[np.isfinite(a)]
+        assert r[0] == len(idx)
+        if len(fin):
+            assert r[1] == float(fin.min()) and r[2] == float(fin.max())
+
+
+def test_failcheck_stops_on_nan(tclb_bin, tmp_path):
+    xml = """<CLBConfig output="output/"><Geometry nx="64" ny="32"><MRT><Box/></MRT><Wall mask="ALL"><Channel/></Wall></Geometry>
+    <Model><Param name="Viscosity" value="-10"/><Param name="GravitationX" value="0.3"/></Model>
+    <Failcheck Iterations="20"/><Solve Iterations="4000"/></CLBConfig>"""
+    (tmp_path / "nan.xml").write_text(xml)
+    r = subprocess.run([tclb_bin, "--gpu", "d2q9", "nan.xml"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "NaN" in r.stdout
