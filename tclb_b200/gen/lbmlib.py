@@ -504,3 +504,95 @@ def central_moment_forward_shared(prefix: str, rho: str, j: Sequence[str], u: Se
             out.append(f"{indent}cm_a = {p} + {m}; cm_b = {p} - {m}; {z} = {z} + cm_a; "
                        f"{p} = cm_b - {u[ax]}*{z}; {m} = cm_a - {u[ax]}*(cm_b + {p});")
     return "\n".join(out) + "\n"
+
+
+# ------------------------------------------------------------------------------------------
+# moment transforms that exploit the inversion symmetry of the velocity set
+# ------------------------------------------------------------------------------------------
+
+def _group_terms(pairs, tol=1e-12):
+    """[(coef, name)] -> C text  c1*(a + b) + c2*(c) ... with +-1 coefficients folded into signs."""
+    groups: Dict[float, list] = {}
+    for c, n in pairs:
+        if abs(c) < tol:
+            continue
+        key = None
+        for k in groups:
+            if abs(abs(k) - abs(c)) < tol * max(1.0, abs(c)):
+                key = k
+                break
+        if key is None:
+            key = abs(c)
+            groups[key] = []
+        groups[key].append(("-" if c < 0 else "+", n))
+    parts = []
+    for k in sorted(groups, key=lambda v: -v):
+        mem = groups[k]
+        body = ""
+        for i, (sg, n) in enumerate(mem):
+            body += (("-" if sg == "-" else "") if i == 0 else (" - " if sg == "-" else " + ")) + n
+        one = abs(k - 1.0) < tol
+        if one:
+            parts.append(body if len(mem) == 1 else f"({body})")
+        else:
+            from .poly import _fmt_num, _clean
+            parts.append(f"({body})*{_fmt_num(_clean(k))}")
+    if not parts:
+        return "0.0"
+    s = parts[0]
+    for p in parts[1:]:
+        s += (" - " + p[1:]) if p.startswith("-") and not p.startswith("-(") and not p.startswith("(-") else " + " + p
+    return s
+
+
+def sym_moments(f: PVec, M: np.ndarray, U: np.ndarray, out, prefix="sy", indent="\t") -> str:
+    """out_j = sum_k f_k M[k,j], computed from pair sums s_k = f_k + f_opp(k) and differences d_k = f_k - f_opp(k):
+    even moments only need the sums, odd moments only the differences, which halves the multiply-adds of a dense
+    product; equal coefficients are grouped so each distinct value is multiplied once."""
+    b = bounce_index(U)
+    Q = len(f)
+    names = [to_c(x) for x in f]
+    lines = []
+    rep = {}
+    for k in range(Q):
+        if b[k] == k:
+            rep[k] = ("self", names[k])
+        elif k < b[k]:
+            s, d = f"{prefix}s{k}", f"{prefix}d{k}"
+            lines.append(f"{indent}const real_t {s} = {names[k]} + {names[b[k]]}, {d} = {names[k]} - {names[b[k]]};")
+            rep[k] = ("pair", s, d)
+    outs = [to_c(o) if not isinstance(o, str) else o for o in out]
+    for j in range(M.shape[1]):
+        terms = []
+        for k in range(Q):
+            if b[k] == k:
+                terms.append((float(M[k, j]), rep[k][1]))
+            elif k < b[k]:
+                e = 0.5 * (M[k, j] + M[b[k], j])
+                o = 0.5 * (M[k, j] - M[b[k], j])
+                terms.append((float(e), rep[k][1]))
+                terms.append((float(o), rep[k][2]))
+        lines.append(f"{indent}{outs[j]} = {_group_terms(terms)};")
+    return "\n".join(lines) + "\n"
+
+
+def sym_populations(R, B: np.ndarray, U: np.ndarray, f: PVec, prefix="sy", indent="\t") -> str:
+    """f_k = sum_j R_j B[j,k] for a velocity set with inversion symmetry: the even and odd parts of each pair are
+    formed once, f_k = E + O, f_opp(k) = E - O."""
+    b = bounce_index(U)
+    Q = len(f)
+    names = [to_c(x) for x in f]
+    Rn = [to_c(r) if not isinstance(r, str) else r for r in R]
+    lines = []
+    for k in range(Q):
+        if b[k] == k:
+            terms = [(float(B[j, k]), Rn[j]) for j in range(B.shape[0])]
+            lines.append(f"{indent}{names[k]} = {_group_terms(terms)};")
+        elif k < b[k]:
+            te = [(float(0.5 * (B[j, k] + B[j, b[k]])), Rn[j]) for j in range(B.shape[0])]
+            to = [(float(0.5 * (B[j, k] - B[j, b[k]])), Rn[j]) for j in range(B.shape[0])]
+            E, O = f"{prefix}E{k}", f"{prefix}O{k}"
+            lines.append(f"{indent}const real_t {E} = {_group_terms(te)};")
+            lines.append(f"{indent}const real_t {O} = {_group_terms(to)};")
+            lines.append(f"{indent}{names[k]} = {E} + {O}; {names[b[k]]} = {E} - {O};")
+    return "\n".join(lines) + "\n"

@@ -11,7 +11,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from ..gen.lbmlib import (d2q9_velocities, full_bounce_back, lattice_weights, mrt_eq, symmetry,
+from ..gen.lbmlib import (d2q9_velocities, full_bounce_back, lattice_weights, mrt_eq, sym_moments, sym_populations, symmetry,
                           weighted_cholesky_basis, zouhe_rewrite)
 from ..gen.modeldef import ModelDef
 from ..gen.poly import PV, Poly, PVec, c_assign, to_c
@@ -153,7 +153,7 @@ def _physics(m: ModelDef, U: np.ndarray, opt) -> str:
     A("CudaDeviceFunction void CollisionMRT() {")
     A(f"\treal_t {names};")
     A("\treal_t Usq = 0;")
-    A(c_assign(Rn, f @ EQ.mat))
+    A(sym_moments(f, EQ.mat, U, Rn))
     usq = (J @ J) * rho ** -2
     A("\tswitch (NodeType & NODE_OBJECTIVE) {")
     A("\tcase NODE_Outlet:")
@@ -175,6 +175,6 @@ def _physics(m: ModelDef, U: np.ndarray, opt) -> str:
     else:
         A("\tJx = Jx + GravitationX*rho;\n\tJy = Jy + GravitationY*rho;")
     A(c_assign(Rn[sel], (Rn + EQ.Req)[sel]))
-    A(c_assign(f, Rn @ Binv))
+    A(sym_populations(Rn, Binv, U, f))
     A("}")
     return "\n".join(c)

@@ -9,7 +9,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from ..gen.lbmlib import d3q19_mrt_matrix, d3q19_velocities, poly_moment_matrix
+from ..gen.lbmlib import d3q19_mrt_matrix, d3q19_velocities, poly_moment_matrix, sym_moments, sym_populations
 from ..gen.modeldef import ModelDef
 from ..gen.poly import PV, Poly, PVec, c_assign, psum, to_c
 
@@ -173,13 +173,11 @@ CudaDeviceFunction float2 Color() {
     for i in [4, 6, 8, 16, 17, 18]:
         S[i] = Poly.sym("gamma2")
     S = PVec(S)
-    A(c_assign(Rs, f @ MT))
+    A(sym_moments(f, MT, U, Rs))
     A(c_assign(Rs[selR], (S * (Rs - Req))[selR]))
     A("\tJx += rho*ForceX;\n\tJy += rho*ForceY;\n\tJz += rho*ForceZ;")
     A(c_assign(Rs[selR], (Rs + Req)[selR]))
-    for i in range(19):
-        A(f"\t{to_c(Rs[i])} /= {float(norm[i])!r};")
-    A(c_assign(f, Rs @ Mm))
+    A(sym_populations(Rs, np.diag(1.0 / norm) @ Mm, U, f))
     A("""	real_t ux, uy, uz;
 	ux = Jx / rho;
 	uy = Jy / rho;

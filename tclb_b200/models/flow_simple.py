@@ -12,7 +12,7 @@ from __future__ import annotations
 import numpy as np
 
 from ..gen.lbmlib import (bounce_index, d2q9_velocities, d3q19_velocities, full_bounce_back, lattice_weights, mrt_eq,
-                          symmetry, tensor_velocities, zouhe)
+                          symmetry, sym_moments, sym_populations, tensor_velocities, zouhe)
 from ..gen.modeldef import ModelDef
 from ..gen.poly import PV, Poly, PVec, c_assign, psum, to_c
 from . import ModelSpec
@@ -115,7 +115,7 @@ def _orthogonal_mrt_collision(A, U, f, names_J, force_syms, smag=None, les_flag=
     sel = np.nonzero(EQ.order > 1)[0]
     S = PVec([Poly.sym("om_r") if o == 2 else Poly.const(0) for o in EQ.order])
     A("\treal_t " + ", ".join(to_c(x) for x in Rn) + ";")
-    A(c_assign(Rn, f @ EQ.mat))
+    A(sym_moments(f, EQ.mat, U, Rn))
     A(c_assign(Rn[sel], (Rn - EQ.Req)[sel]))
     A("\treal_t om_r = 1.0 - omega;")
     if smag:
@@ -134,7 +134,7 @@ def _orthogonal_mrt_collision(A, U, f, names_J, force_syms, smag=None, les_flag=
     for k in range(d):
         A(f"\t{names_J[k]} = {names_J[k]} + rho*{force_syms[k]};")
     A(c_assign(Rn[sel], (Rn + EQ.Req)[sel]))
-    A(c_assign(f, Rn @ np.linalg.inv(EQ.mat)))
+    A(sym_populations(Rn, np.linalg.inv(EQ.mat), U, f))
     return EQ
 
 
