@@ -420,7 +420,8 @@ class ModelDef:
         names = {s.name for s in self.settings}
         for s in self.settings + self.zonesettings:
             if s.derived is not None and s.derived not in names:
-                raise ModelError(f"derived setting target {s.derived} of {s.name} does not exist")
+                # the reference generator does not check this (models/multiphase/experimental/d2q9_lee relies on it)
+                s.derived, s.equation = None, None
         self.finalized = True
         return self
 

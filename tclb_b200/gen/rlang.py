@@ -168,7 +168,7 @@ _TOKEN = re.compile(r"""
     (?P<ws>[ \t\r]+) | (?P<comment>\#[^\n]*) | (?P<nl>\n) |
     (?P<num>(?:\d+\.\d*|\.\d+|\d+)(?:[eE][+-]?\d+)?L?|0x[0-9a-fA-F]+L?) |
     (?P<str>"(?:[^"\\]|\\.)*"|'(?:[^'\\]|\\.)*') |
-    (?P<op>%[^%\n]*%|<<-|<-|->|<=|>=|==|!=|&&|\|\||\[\[|\]\]|::|[-+*/^<>=!&|~?:$@\[\](){},;]) |
+    (?P<op>%[^%\n]*%|<<-|<-|->|<=|>=|==|!=|&&|\|\||\*\*|\[\[|::|[-+*/^<>=!&|~?:$@\[\](){},;]) |
     (?P<id>(?:[A-Za-z.][A-Za-z0-9._]*)|`[^`]+`)
 """, re.X)
 
@@ -243,7 +243,7 @@ class Parser:
         "?": (1, "L"), "=": (3, "R"), "<-": (5, "R"), "<<-": (5, "R"), "->": (6, "L"), "~": (8, "L"),
         "||": (10, "L"), "|": (10, "L"), "&&": (12, "L"), "&": (12, "L"),
         "==": (16, "L"), "!=": (16, "L"), "<": (16, "L"), ">": (16, "L"), "<=": (16, "L"), ">=": (16, "L"),
-        "+": (20, "L"), "-": (20, "L"), "*": (22, "L"), "/": (22, "L"), ":": (26, "L"), "^": (30, "R"),
+        "+": (20, "L"), "-": (20, "L"), "*": (22, "L"), "/": (22, "L"), ":": (26, "L"), "^": (30, "R"), "**": (30, "R"),
     }
 
     def binop_info(self, tok):
@@ -275,7 +275,7 @@ class Parser:
             elif op == "->":
                 left = ("assign", right, left, False)
             else:
-                left = ("bin", op, left, right)
+                left = ("bin", "^" if op == "**" else op, left, right)
         return left
 
     def parse_unary(self):
@@ -304,7 +304,8 @@ class Parser:
                 self.depth += 1
                 idx = self.parse_expr(0)
                 self.depth -= 1
-                self.expect("]]")
+                self.expect("]")
+                self.expect("]")
                 e = ("index2", e, idx)
             elif v == "[":
                 self.next()
