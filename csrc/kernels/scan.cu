@@ -134,3 +134,79 @@ extern "C" int tclb_scan_array(const void *dev_ptr, long long n, int real_size, 
     }
     return launch_scan(dev_ptr, n, real_size, (cudaStream_t)stream, scratch, n_blocks, result3_dev);
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Scan entry point that allocates nothing (declared in include/tclb_b200.h; no counterpart in the reference).
+//
+// Same k_scan kernel, but the partials and the arrival counter live in a fixed array that is part of this library's
+// device image, so nothing is obtained from the CUDA allocator or any other allocating routine, on the first call or
+// later.  The array is sized for TCLB_SCAN_STATIC_MAX_ELEMS elements; longer inputs are refused.
+//
+// Layout of the array: bytes [0,256) hold the arrival counter (one unsigned), the partials start at byte 256.
+//   * the counter must be 0 when the kernel starts: every call clears it with a memset ordered on the caller's
+//     stream ahead of the launch, so a call that was cut short earlier cannot poison the next one;
+//   * the partials keep whatever the previous call left there; each block writes its own slot before the last block
+//     reads slots [0, n_blocks), so stale slots are never read.
+// There is ONE array per device and every call on that device uses it: two calls whose work can overlap on the GPU
+// (different streams without an ordering between them, or two host threads) race on it and return garbage.
+namespace {
+
+constexpr long long SCAN_STATIC_MAX_BLOCKS = 16384;
+constexpr long long SCAN_STATIC_MAX_ELEMS = SCAN_STATIC_MAX_BLOCKS * SCAN_CHUNK;       // 67,108,864 elements
+constexpr size_t SCAN_STATIC_HEADER = 256;
+constexpr size_t SCAN_STATIC_BYTES = SCAN_STATIC_HEADER + (size_t)SCAN_STATIC_MAX_BLOCKS * sizeof(Partial);   // 393,472 B
+
+static __device__ __align__(256) unsigned char g_scan_static[SCAN_STATIC_BYTES];
+
+// address of g_scan_static on each device, looked up once per device (first call there) with that device current
+void *g_scan_static_ptr[64] = {};
+std::mutex g_scan_static_mu;
+
+int scan_static_fail(char *err, int err_cap, int code, const char *fmt, long long a = 0, long long b = 0) {
+    if (err && err_cap > 0) snprintf(err, (size_t)err_cap, fmt, a, b);
+    return code;
+}
+
+}  // namespace
+
+static_assert(SCAN_STATIC_MAX_ELEMS == TCLB_SCAN_STATIC_MAX_ELEMS, "header and kernel disagree on the static scan limit");
+
+extern "C" int tclb_scan_array_static(const void *dev_ptr, long long n, int real_size, void *stream, double *result3_dev,
+                                      char *err, int err_cap) {
+    if (err && err_cap > 0) err[0] = 0;
+    if (!dev_ptr || !result3_dev || n <= 0)
+        return scan_static_fail(err, err_cap, -1, "tclb_scan_array_static: empty input or missing output (n=%lld)", n);
+    if (real_size != 4 && real_size != 8)
+        return scan_static_fail(err, err_cap, -2, "tclb_scan_array_static: real_size must be 4 or 8, got %lld", real_size);
+    if (n > SCAN_STATIC_MAX_ELEMS)
+        return scan_static_fail(err, err_cap, -3, "tclb_scan_array_static: n=%lld exceeds the fixed scratch limit of %lld elements; "
+                                                  "use tclb_scan_array for longer arrays", n, SCAN_STATIC_MAX_ELEMS);
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64)
+        return scan_static_fail(err, err_cap, -4, "tclb_scan_array_static: no usable current CUDA device (device %lld, CUDA error %lld)", dev, (long long)e);
+    void *scratch;
+    {
+        std::lock_guard<std::mutex> lk(g_scan_static_mu);
+        if (!g_scan_static_ptr[dev]) {
+            // set-up, once per device, with that device current
+            void *p = nullptr;
+            e = cudaGetSymbolAddress((void **)&p, g_scan_static);
+            if (e != cudaSuccess || !p)
+                return scan_static_fail(err, err_cap, -5, "tclb_scan_array_static: cudaGetSymbolAddress failed on device %lld (CUDA error %lld)", dev, (long long)e);
+            g_scan_static_ptr[dev] = p;
+        }
+        scratch = g_scan_static_ptr[dev];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned *counter = (unsigned *)scratch;
+    Partial *partials = (Partial *)((char *)scratch + SCAN_STATIC_HEADER);
+    const unsigned n_blocks = (unsigned)((n + SCAN_CHUNK - 1) / SCAN_CHUNK);
+    if ((e = cudaMemsetAsync(counter, 0, sizeof(unsigned), st)) != cudaSuccess)
+        return scan_static_fail(err, err_cap, -6, "tclb_scan_array_static: clearing the arrival counter failed (CUDA error %lld)", (long long)e);
+    if (real_size == 4) k_scan<float><<<n_blocks, SCAN_THREADS, 0, st>>>((const float *)dev_ptr, n, partials, counter, result3_dev);
+    else k_scan<double><<<n_blocks, SCAN_THREADS, 0, st>>>((const double *)dev_ptr, n, partials, counter, result3_dev);
+    if ((e = cudaGetLastError()) != cudaSuccess)
+        return scan_static_fail(err, err_cap, -7, "tclb_scan_array_static: kernel launch failed (CUDA error %lld)", (long long)e);
+    return 0;
+}

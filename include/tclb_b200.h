@@ -78,6 +78,27 @@ int tclb_domain_set_hooks(tclb_domain_h *, tclb_exchange_fn ex, tclb_reduce_fn r
 int tclb_scan_array(const void *dev_ptr, long long n, int real_size, void *stream, double *result3_dev);
 const char *tclb_scan_last_error(void);
 
+/* ---- device scan without any allocation (no counterpart in the reference) ----
+ * Same result as tclb_scan_array, for callers that must not allocate: code running between the begin and end of a
+ * region where the CUDA allocator is off limits (a memory-pool or allocator that is being replaced or audited,
+ * a real-time loop with a fixed memory budget, a plugin that the host application forbids from calling cudaMalloc).
+ * The scratch the kernel needs is a fixed array inside the library's device image (393,472 bytes per device), so the
+ * call never asks CUDA, the C++ runtime or torch for memory; the caller supplies the input, the 3-double result buffer
+ * and, optionally, a buffer for the error text.
+ *   - n must be 1 .. TCLB_SCAN_STATIC_MAX_ELEMS; anything longer returns -3 with a message naming the limit.
+ *   - The first call on each device looks up the device address of the array (that device must be current, as for
+ *     every call).  Make that first call on each device before any stream capture starts.
+ *   - All calls on a device share the one array.  Calls are safe back to back on one stream, or on streams ordered by
+ *     events; calls that can run concurrently on the same device (unordered streams, several host threads) race on the
+ *     array and give wrong results.  The array keeps the previous call's partial results; the only part that has to
+ *     start at zero (an arrival counter) is cleared by every call on `stream` before the kernel.
+ * Returns 0 on success, a negative code otherwise (-1 bad arguments, -2 bad real_size, -3 too long, -4 no device,
+ * -5 symbol lookup failed, -6 counter clear failed, -7 launch failed); if err != NULL the reason is written there
+ * (at most err_cap bytes, always terminated). */
+#define TCLB_SCAN_STATIC_MAX_ELEMS 67108864LL
+int tclb_scan_array_static(const void *dev_ptr, long long n, int real_size, void *stream, double *result3_dev,
+                           char *err, int err_cap);
+
 /* ---- units (reference src/unit.{h,cpp}) ---- */
 typedef struct tclb_units_h tclb_units_h;
 tclb_units_h *tclb_units_create(void);
