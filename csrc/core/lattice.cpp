@@ -39,7 +39,16 @@ Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &loca
     int sg = arena_.reserve(sizeof(double) * TCLB_GL_SLOTS * std::max(1, m->d->n_globals), "globals");
     int ss = arena_.reserve(sizeof(unsigned) * 64, "halo flags");
     int sr = arena_.reserve(sizeof(double) * TCLB_GL_RING * TCLB_MAX_RANKS * (std::max(1, m->d->n_globals) + 1), "globals ring");
+    // one Globals partial per warp of a stage launch: sized for the block shape with the most blocks
+    gl_partial_stride_ = 0;
+    if (backend == TCLB_BACKEND_CUDA)
+        for (int bx : {32, 64, 128}) {
+            const int by = 128 / bx;
+            gl_partial_stride_ = std::max(gl_partial_stride_, 4LL * ((nx + bx - 1) / bx) * ((ny + by - 1) / by) * nz);   // 4 warps per block
+        }
+    int sp = arena_.reserve((size_t)gl_partial_stride_ * std::max(1, m->d->n_globals) * m->real_size(), "globals partials");
     arena_.finalize();
+    gl_partial_ = gl_partial_stride_ > 0 ? arena_.ptr(sp) : nullptr;
     gl_ring_ = (double *)arena_.ptr(sr);
     snap_[0] = arena_.ptr(s0); snap_[1] = arena_.ptr(s1);
     flags_ = arena_.ptr(sf);
@@ -239,6 +248,15 @@ void Lattice::upload_zone_table_if_dirty() {
     int stride = zs.zones();
     std::vector<double> tab;
     zs.build_table(tab, stride);
+    {
+        // table layout [len][n_zonesettings][stride]; the <Global>InObj weights are the settings from in_obj_offset on
+        const int ns = zs.n_settings(), first = model->d->in_obj_offset, ng = model->d->sum_globals;
+        obj_enabled_ = false;
+        for (int t = 0; t < zs.len() && !obj_enabled_; t++)
+            for (int s = std::max(0, first); s < std::min(ns, first + ng) && !obj_enabled_; s++)
+                for (int z = 0; z < stride; z++)
+                    if (tab[((size_t)t * ns + s) * stride + z] != 0.0) { obj_enabled_ = true; break; }
+    }
     const int rs = model->real_size();
     size_t bytes = std::max<size_t>(tab.size(), 1) * rs;
     if (bytes > zone_dev_bytes_) {
@@ -285,6 +303,7 @@ void Lattice::fill_launch(tclb_launch_t &L) const {
     L.st_modes = (const tclb_st_mode_t *)st_dev_; L.st_n = st_n_;
     L.block_x = block_x; L.block_y = block_y;
     L.scale = 1.0;
+    L.obj_enabled = obj_enabled_ ? 1 : 0;
 }
 void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode, bool publish) {
     upload_zone_table_if_dirty();
@@ -299,6 +318,7 @@ void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode, bool
     L.sig_enable = (sig_enable && halo_mode == TCLB_HALO_DIRECT) ? 1 : 0;
     L.sig_count = sig_ + 9;
     L.gl_counter = gl_counter_;
+    L.gl_partial = gl_partial_; L.gl_partial_stride = gl_partial_stride_;
     L.gl_epoch = epoch;
     L.gl_publish = (gmode != TCLB_GLOBALS_NONE && publish) ? 1 : 0;
     if (gl_complete) {

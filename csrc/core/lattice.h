@@ -116,10 +116,13 @@ class Lattice {
     double *globals_dev_;
     double *gl_ring_;
     unsigned *gl_counter_;
-    unsigned *sig_;                // [0..8] flags_in, [9] arrival counter
+    void *gl_partial_;             // real_t[n_globals][gl_partial_stride_]: per-block Globals partials of a stage launch
+    long long gl_partial_stride_;
+    unsigned *sig_;               // [0..8] flags_in, [9] arrival counter
     void *zone_dev_;
     size_t zone_dev_bytes_;
     int zone_stride_;
+    bool obj_enabled_ = true;      // any <Global>InObj weight non-zero (refreshed with the zone table)
     void *cuts_dev_;
     void *st_dev_;
     int st_n_;

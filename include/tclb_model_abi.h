@@ -12,7 +12,7 @@
 extern "C" {
 #endif
 
-#define TCLB_ABI_VERSION 5
+#define TCLB_ABI_VERSION 6
 #define TCLB_MAX_NEIGH 9            /* (dy,dz) in {-1,0,1}^2 ; x is never decomposed */
 #define TCLB_MAX_RANKS 16           /* subdomains that exchange Globals through peer memory (one box) */
 #define TCLB_GL_RING 8              /* depth of the Globals publication ring */
@@ -60,12 +60,15 @@ typedef struct {
     int gl_publish, gl_rank, gl_nranks;
     double *gl_ring[TCLB_MAX_RANKS];
     unsigned *gl_counter;
+    void *gl_partial;                   /* real_t[n_globals][gl_partial_stride]: one partial per warp of a stage launch */
+    long long gl_partial_stride;        /* capacity in warps (>= warps of any launch) */
     unsigned gl_epoch;
     const double *settings;             /* host array [n_settings] */
     const void *zone_table;             /* real_t[zone_len][n_zonesettings][zone_stride] */
     int zone_len, zone_index, zone_stride;
     int iter, reset_iter;
     int globals_mode, halo_mode;
+    int obj_enabled;                    /* 0: every <Global>InObj weight is zero in every zone, the kernels skip the Objective terms */
     void *halo_snap[TCLB_MAX_NEIGH];    /* snapshot that receives my border rows, index (dy+1)+3(dz+1) */
     int halo_ny[TCLB_MAX_NEIGH], halo_nz[TCLB_MAX_NEIGH];
     /* fused halo signalling (sequence numbers, see csrc/core/lattice.cpp) */

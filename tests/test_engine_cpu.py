@@ -113,3 +113,24 @@ def test_cumulant_central_equals_raw_formulation():
         res.append((d.get_quantity("U"), d.get_quantity("P")))
     assert np.abs(res[0][0] - res[1][0]).max() < 1e-13
     assert np.abs(res[0][1] - res[1][1]).max() < 1e-13
+
+
+def test_objective_weights_switch_on_with_zone_settings():
+    """<Global>InObj weights: Objective gets the zone's weight once per contribution (reference
+    src/cuda.cu.Rt:113-119); with every weight zero the kernels skip the terms and Objective stays 0."""
+    from tclb_b200.runtime import Domain, Model
+    m = Model("d3q27_cumulant", "double")
+    shape = (32, 20, 16)
+    d = Domain(m, shape, "cpu", nranks=2)
+    setup_case(d, m, shape)
+    d.iterate(3, globals_every=True)
+    assert d.globals()["Objective"] == 0.0
+    fluid = int((d.get_flags() & m.nodetypes["MRT"][1] == m.nodetypes["MRT"][0]).sum())
+    d.set_setting("MassInObj", 0.25)
+    d.set_setting("FluxInObj", 2.0)
+    d.iterate(1, globals_every=True)
+    assert abs(d.globals()["Objective"] - 2.25 * fluid) < 1e-9 * fluid
+    d.set_setting("MassInObj", 0.0)
+    d.set_setting("FluxInObj", 0.0)
+    d.iterate(1, globals_every=True)
+    assert d.globals()["Objective"] == 0.0
