@@ -39,12 +39,12 @@ Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &loca
     int sg = arena_.reserve(sizeof(double) * TCLB_GL_SLOTS * std::max(1, m->d->n_globals), "globals");
     int ss = arena_.reserve(sizeof(unsigned) * 64, "halo flags");
     int sr = arena_.reserve(sizeof(double) * TCLB_GL_RING * TCLB_MAX_RANKS * (std::max(1, m->d->n_globals) + 1), "globals ring");
-    // one Globals partial per warp of a stage launch: sized for the block shape with the most blocks
+    // one Globals partial per thread block of a stage launch: sized for the block shape with the most blocks
     gl_partial_stride_ = 0;
     if (backend == TCLB_BACKEND_CUDA)
         for (int bx : {32, 64, 128}) {
             const int by = 128 / bx;
-            gl_partial_stride_ = std::max(gl_partial_stride_, 4LL * ((nx + bx - 1) / bx) * ((ny + by - 1) / by) * nz);   // 4 warps per block
+            gl_partial_stride_ = std::max(gl_partial_stride_, 4LL * ((nx + bx - 1) / bx) * ((ny + by - 1) / by) * nz);
         }
     int sp = arena_.reserve((size_t)gl_partial_stride_ * std::max(1, m->d->n_globals) * m->real_size(), "globals partials");
     arena_.finalize();

@@ -60,8 +60,8 @@ typedef struct {
     int gl_publish, gl_rank, gl_nranks;
     double *gl_ring[TCLB_MAX_RANKS];
     unsigned *gl_counter;
-    void *gl_partial;                   /* real_t[n_globals][gl_partial_stride]: one partial per warp of a stage launch */
-    long long gl_partial_stride;        /* capacity in warps (>= warps of any launch) */
+    void *gl_partial;                   /* real_t[n_globals][gl_partial_stride]: one partial per thread block of a stage launch */
+    long long gl_partial_stride;        /* capacity in blocks (>= blocks of any launch) */
     unsigned gl_epoch;
     const double *settings;             /* host array [n_settings] */
     const void *zone_table;             /* real_t[zone_len][n_zonesettings][zone_stride] */

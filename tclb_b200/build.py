@@ -12,6 +12,7 @@ import concurrent.futures as cf
 import hashlib
 import json
 import os
+import threading
 import shutil
 import subprocess
 import sys
@@ -120,15 +121,23 @@ def build_core(force: bool = False, verbose: bool = False) -> Path:
     return target
 
 
+_GEN_LOCK = threading.Lock()
+
+
 def generate_model(variant: str) -> Path:
     from .gen.emit import emit_model_source
     from .models import build_model
     GENDIR.mkdir(parents=True, exist_ok=True)
-    m = build_model(variant)
-    src = emit_model_source(m, variant)
     out = GENDIR / f"{variant}.cu"
-    if not out.exists() or out.read_text() != src:
-        out.write_text(src)
+    # one generation at a time: the symbolic layer numbers its temporaries with a per-model counter, and the
+    # float and double builds of a model (separate threads in build_all) share this file
+    with _GEN_LOCK:
+        m = build_model(variant)
+        src = emit_model_source(m, variant)
+        if not out.exists() or out.read_text() != src:
+            tmp = out.with_suffix(".cu.tmp")
+            tmp.write_text(src)
+            os.replace(tmp, out)
     return out
 
 

@@ -477,9 +477,12 @@ def central_moment_backward(prefix: str, u: Sequence[str], indent="\t") -> str:
     return "\n".join(out) + "\n"
 
 
-def central_moment_forward_shared(prefix: str, rho: str, j: Sequence[str], u: Sequence[str], irho: str, indent="\t") -> str:
+def central_moment_forward_shared(prefix: str, rho: str, j: Sequence[str], u: Sequence[str], irho: str, indent="\t",
+                                  after_velocity: str = "") -> str:
     """Forward central-moment transform that also produces density and momentum from the partial sums of
-    its own first (x) pass: rho and J cost 8+8+5+5 additions instead of 26+3*17."""
+    its own first (x) pass: rho and J cost 8+8+5+5 additions instead of 26+3*17.
+    `after_velocity` is code placed right after rho, J and u exist and before the sweeps need registers for their
+    temporaries (the place for Globals that only need density and velocity)."""
     out = [f"{indent}real_t cm_a, cm_b;"]
     ax = 0
     for jj, k in product(range(3), repeat=2):
@@ -495,6 +498,8 @@ def central_moment_forward_shared(prefix: str, rho: str, j: Sequence[str], u: Se
     out.append(f"{indent}real_t {j[2]} = (({nm(0,0,1)} - {nm(0,0,2)}) + ({nm(0,1,1)} - {nm(0,1,2)})) + ({nm(0,2,1)} - {nm(0,2,2)});")
     out.append(f"{indent}real_t {irho} = 1.0/{rho};")
     out.append(f"{indent}{u[0]} = {j[0]}*{irho}; {u[1]} = {j[1]}*{irho}; {u[2]} = {j[2]}*{irho};")
+    if after_velocity:
+        out.append(after_velocity.rstrip("\n"))
     for jj, k in product(range(3), repeat=2):
         z, p, m = _triple_names(prefix, ax, jj, k)
         out.append(f"{indent}cm_b = {p}; {p} = cm_b - {u[0]}*{z}; {m} = {m} - {u[0]}*(cm_b + {p});")

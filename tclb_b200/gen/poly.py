@@ -383,8 +383,37 @@ def PV(*parts) -> PVec:
     return PVec(out)
 
 
-def c_assign(lhs, rhs, op: str = "=", indent: str = "\t", decl: str = "") -> str:
-    """Emit ``lhs = rhs;`` lines (vectorised), the analogue of the reference's ``C()``."""
+_tmp_counter = [0]
+
+
+def _terms_c(p: Poly, mono_text) -> str:
+    """to_c with the text of every monomial supplied by mono_text(mono) -> (numerator text, denominator text)."""
+    if p.is_zero():
+        return "0.0"
+    parts: List[str] = []
+    for m, c in sorted(p.t.items(), key=lambda kv: (len(kv[0]), kv[0])):
+        num, den = mono_text(m)
+        neg = (c < 0)
+        ac = -c if neg else c
+        one = (ac == 1) if isinstance(ac, (int, Fraction)) else abs(ac - 1.0) < 1e-15
+        if num:
+            body = num if one else f"{num}*{_fmt_num(ac)}"
+        else:
+            body = _fmt_num(ac)
+        if den:
+            body = f"{body}/({den})" if "*" in den else f"{body}/{den}"
+        parts.append((("-" if neg else "") if not parts else (" - " if neg else " + ")) + body)
+    return "".join(parts)
+
+
+def c_assign(lhs, rhs, op: str = "=", indent: str = "\t", decl: str = "", optimize: bool = True) -> str:
+    """Emit ``lhs = rhs;`` lines (vectorised), the analogue of the reference's ``C()``.
+
+    With ``optimize`` the block is rewritten for the instruction count of the GPU: a division costs ~10 issue
+    slots in fp32 (more in fp64), so every symbol that only appears as a divisor gets ONE reciprocal up front and
+    the divisions become multiplications, and a product of symbols used by several terms of the block is formed
+    once.  Only symbols that the block itself does not assign are touched, so the meaning is unchanged (up to the
+    rounding of x/r versus x*(1/r))."""
     if isinstance(lhs, (Poly, str)):
         lhs = [lhs]
     if isinstance(rhs, (Poly, str, int, float, Fraction)):
@@ -392,8 +421,55 @@ def c_assign(lhs, rhs, op: str = "=", indent: str = "\t", decl: str = "") -> str
     lhs = list(lhs)
     rhs = list(rhs)
     assert len(lhs) == len(rhs), (len(lhs), len(rhs))
-    lines = []
-    for l, r in zip(lhs, rhs):
-        ls = l if isinstance(l, str) else to_c(l)
-        lines.append(f"{indent}{decl}{ls} {op} {to_c(r)};")
+    names = [l if isinstance(l, str) else to_c(l) for l in lhs]
+    if not optimize or any(isinstance(r, str) for r in rhs):
+        return "\n".join(f"{indent}{decl}{ls} {op} {r if isinstance(r, str) else to_c(r)};" for ls, r in zip(names, rhs)) + "\n"
+    polys = [Poly.lift(r) for r in rhs]
+    assigned = set(names)
+    # ---- reciprocals of divisor symbols the block does not assign ----
+    divisors: List[str] = []
+    for p in polys:
+        for m in p.t:
+            for s, e in m:
+                if e < 0 and s not in assigned and s not in divisors:
+                    divisors.append(s)
+    pre: List[str] = []
+    rcp: Dict[str, str] = {}
+    for s in divisors:
+        _tmp_counter[0] += 1
+        rcp[s] = f"rcp{_tmp_counter[0]}_"
+        pre.append(f"{indent}real_t {rcp[s]}; {rcp[s]} = 1.0/{s};")
+
+    def factors(m: Mono) -> Tuple[List[str], List[str]]:
+        num: List[str] = []
+        den: List[str] = []
+        for s, e in m:
+            if e > 0:
+                num.extend([s] * e)
+            elif s in rcp:
+                num.extend([rcp[s]] * (-e))
+            else:
+                den.extend([s] * (-e))
+        return num, den
+
+    # ---- products shared by several terms ----
+    uses: Dict[Mono, int] = {}
+    for p in polys:
+        for m in p.t:
+            uses[m] = uses.get(m, 0) + 1
+    shared: Dict[Mono, str] = {}
+    for m, n in uses.items():
+        num, den = factors(m)
+        if n >= 2 and not den and len(num) >= 2 and not any(s in assigned for s, _ in m):
+            _tmp_counter[0] += 1
+            shared[m] = f"mon{_tmp_counter[0]}_"
+            pre.append(f"{indent}real_t {shared[m]}; {shared[m]} = {'*'.join(num)};")
+
+    def mono_text(m: Mono) -> Tuple[str, str]:
+        if m in shared:
+            return shared[m], ""
+        num, den = factors(m)
+        return "*".join(num), "*".join(den)
+
+    lines = pre + [f"{indent}{decl}{ls} {op} {_terms_c(p, mono_text)};" for ls, p in zip(names, polys)]
     return "\n".join(lines) + "\n"

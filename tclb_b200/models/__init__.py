@@ -80,6 +80,8 @@ def variants(base: str) -> List[str]:
 
 def build_model(variant: str):
     base, opts = split_variant(variant)
+    from ..gen import poly
+    poly._tmp_counter[0] = 0          # temporaries of generated code are numbered per model: same source every time
     m = specs()[base].build(opts)
     m.name = base
     m.finalize()

@@ -85,7 +85,9 @@ def build(options=None, collision="central") -> ModelDef:
     m.AddNodeType(name="MRT", group="COLLISION")
     m.code = _physics(m, U, fname, opt, collision)
     # measured on B200 (profiles/): 64 registers/thread -> 8 blocks of 128 threads per SM is the fastest fp32 build
-    m.tuning = dict(min_blocks_float=8, min_blocks_double=3)
+    # measured on B200 (1024x512x512 fp32): plain kernel 64 regs/8 blocks 28.8 GLUPS (72 regs: 24.9, 80: 23.9);
+    # Globals kernel 80 regs/6 blocks 24.3 GLUPS (64 regs: 20.8-23.3, 72: 22.4, 96: 18.9)
+    m.tuning = dict(min_blocks_float=8, min_blocks_double=3, min_blocks_g_float=6)
     return m
 
 
@@ -346,19 +348,19 @@ def _collision_central(A, opt, jx="0", jy="0", jz="0"):
     formed.  The first-order shift by the body force enters as the velocity of the backward sweep."""
     A("CudaDeviceFunction void CollisionMRT() {")
     A("	vector_t u0;      // momentum/density without the half-force shift: the first raw cumulant")
-    A(central_moment_forward_shared("f", "rho", ["jx", "jy", "jz"], ["u0.x", "u0.y", "u0.z"], "irho"))
-    A("""	{
-		vector_t velocity;      // what the quantity U reports: half-force shifted, zero on walls
-		if ((NodeType & NODE_BOUNDARY) == NODE_Wall) { velocity.x = 0; velocity.y = 0; velocity.z = 0; }
-		else { velocity.x = u0.x + ForceX*0.5*irho; velocity.y = u0.y + ForceY*0.5*irho; velocity.z = u0.z + ForceZ*0.5*irho; }
+    # the Globals only need density and velocity: they are accumulated right after those exist, before the sweeps
+    # (the point of highest register pressure comes later); momentum is rho*velocity = J + F/2 off the walls
+    globals_block = """	{
+		const bool wall_ = (NodeType & NODE_BOUNDARY) == NODE_Wall;
 		AddToDensity( rho );
-		AddToFlux( velocity.x );
 		AddToMass( rho );
-		AddToXMomentum( rho * velocity.x );
-		AddToYMomentum( rho * velocity.y );
-		AddToZMomentum( rho * velocity.z );
-	}
-	real_t w0 = 1.0/(3*nu+0.5), w1 = 1.0;
+		AddToFlux( wall_ ? (real_t)0 : u0.x + ForceX*0.5*irho );
+		AddToXMomentum( wall_ ? (real_t)0 : jx + ForceX*0.5 );
+		AddToYMomentum( wall_ ? (real_t)0 : jy + ForceY*0.5 );
+		AddToZMomentum( wall_ ? (real_t)0 : jz + ForceZ*0.5 );
+	}"""
+    A(central_moment_forward_shared("f", "rho", ["jx", "jy", "jz"], ["u0.x", "u0.y", "u0.z"], "irho", after_velocity=globals_block))
+    A("""	real_t w0 = 1.0/(3*nu+0.5), w1 = 1.0;
 	if ((NodeType & NODE_BOUNDARY) != 0) w0 = 1.0/(3*nubuffer+0.5);""")
     second = ["200", "020", "002", "110", "101", "011"]
     third = ["210", "201", "120", "021", "102", "012", "111", "300"]

@@ -100,6 +100,8 @@ def test_cumulant_central_equals_raw_formulation():
     from tclb_b200 import build
     from tclb_b200.models import flow_d3q27_cumulant as M
     from tclb_b200.runtime import Domain, Model
+    from tclb_b200.gen import poly
+    poly._tmp_counter[0] = 0          # same generated source on every run: the cached library is reused
     build.build_custom(M.build(collision="raw"), "d3q27_cumulant_rawref", "double")
     res = []
     for name in ["d3q27_cumulant", "d3q27_cumulant_rawref"]:

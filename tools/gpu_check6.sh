@@ -12,11 +12,11 @@ echo "== d3q19 noglob"; timeout 600 python bench.py --steps 15 --warmup 3 --mode
 echo "== ncu"
 CMD="python bench.py --steps 3 --warmup 3 --shape 512,256,256"
 $CMD > gpurun_out/plain_a.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 40 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
-$CMD > gpurun_out/plain_b.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_stage -s 3 -c 1 -o gpurun_out/prof_cumulant8 $CMD > gpurun_out/ncu_full.log 2>&1
+$CMD > gpurun_out/plain_b.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_stage -s 3 -c 1 -o gpurun_out/prof_cumulant9 $CMD > gpurun_out/ncu_full.log 2>&1
 tail -2 gpurun_out/ncu_full.log
 CMD="python bench.py --steps 3 --warmup 3 --shape 512,256,256 --no-globals"
-$CMD > gpurun_out/plain_c.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_stage -s 3 -c 1 -o gpurun_out/prof_cumulant8_noglob $CMD > gpurun_out/ncu_full2.log 2>&1
+$CMD > gpurun_out/plain_c.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_stage -s 3 -c 1 -o gpurun_out/prof_cumulant9_noglob $CMD > gpurun_out/ncu_full2.log 2>&1
 tail -2 gpurun_out/ncu_full2.log
 CMD="python bench.py --steps 3 --warmup 3 --shape 512,512,256 --model d3q19 --no-globals"
-$CMD > gpurun_out/plain_d.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_stage -s 3 -c 1 -o gpurun_out/prof_d3q19b $CMD > gpurun_out/ncu_full3.log 2>&1
+$CMD > gpurun_out/plain_d.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_stage -s 3 -c 1 -o gpurun_out/prof_d3q19c $CMD > gpurun_out/ncu_full3.log 2>&1
 tail -2 gpurun_out/ncu_full3.log
