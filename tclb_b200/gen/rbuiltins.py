@@ -263,6 +263,8 @@ def install(I):
     G.set("nlevels", lambda I, a, k: vec(0))
     G.set("rows", lambda I, a, k: _rows(a[0]))
     G.set("pi", vec(math.pi))
+    G.set("T", vec(True))       # ordinary variables in R: models do assign to F and T
+    G.set("F", vec(False))
     G.set("letters", vec(list("abcdefghijklmnopqrstuvwxyz")))
     G.set("LETTERS", vec(list("ABCDEFGHIJKLMNOPQRSTUVWXYZ")))
 
@@ -308,6 +310,9 @@ def install(I):
         return vec(n) if n else NULL
 
     def _t(x):
+        from .poly import PVec as _PV
+        if isinstance(x, _PV):
+            return x
         if isinstance(x, DataFrame):
             x = _as_matrix(x)
         v = vec(x)
@@ -547,7 +552,7 @@ def install(I):
     @bi("sprintf")
     def _sprintf(I, a, k):
         fmt = to_str(scalar(a[0]))
-        args = [vec(x).tolist() for x in a[1:]]
+        args = [vec(x).ravel(order="F").tolist() for x in a[1:]]
         n = max([len(x) for x in args] + [1])
         out = []
         for i in range(n):
@@ -668,6 +673,46 @@ def install_poly(I):
     G.set("subst", _subst)
     G.set("is.zero", lambda I, a, k: (np.array([p.is_zero() for p in a[0]], dtype=bool) if isinstance(a[0], PVec) else vec(a[0].is_zero()) if isinstance(a[0], Poly)
                                       else vec(a[0]) == 0))
+
+    def _gapply(I, a, k):
+        """gvector::gapply: apply FUN to every element of a symbolic vector; simplify=TRUE returns a plain vector"""
+        x, fn = a[0], a[1]
+        simp = truthy(k.get("simplify", vec(False)))
+        items = list(x) if isinstance(x, PVec) else [x]
+        res = [I.call(fn, [it], OrderedDict()) for it in items]
+        if simp:
+            flat = []
+            for r in res:
+                r = vec(r)
+                flat.extend(r.ravel().tolist() if r.size else [0.0])
+            return vec(flat)
+        if all(isinstance(r, Poly) for r in res):
+            return PVec(res)
+        return RList.make(res)
+    G.set("gapply", _gapply)
+
+    def _append(I, a, k):
+        x, values = a[0], a[1]
+        after = int(scalar(k["after"])) if "after" in k else None
+        if isinstance(x, RList) or isinstance(values, RList):
+            xs = list(x.items()) if isinstance(x, RList) else [(f"\x00a{i}", v) for i, v in enumerate(_flat([x]))]
+            vs = list(values.items()) if isinstance(values, RList) else [(f"\x00b{i}", v) for i, v in enumerate(_flat([values]))]
+            allv = xs + vs if after is None else xs[:after] + vs + xs[after:]
+            return RList.make([v for _, v in allv], [n if not n.startswith("\x00") else "" for n, _ in allv])
+        xs, vs = _flat([x]) if x is not NULL else [], _flat([values]) if values is not NULL else []
+        return vec(xs + vs if after is None else xs[:after] + vs + xs[after:])
+    G.set("append", _append)
+
+    def _replace(I, a, k):
+        x = vec(a[0]).copy()
+        idx = vec(a[1])
+        vals = vec(a[2])
+        flat = x.ravel(order="F")
+        pos = np.nonzero(idx)[0] if idx.dtype == bool else (idx.astype(int) - 1)
+        for j, p_ in enumerate(pos.tolist()):
+            flat[p_] = vals.ravel()[j % vals.size]
+        return flat.reshape(x.shape, order="F")
+    G.set("replace", _replace)
     G.set("provideDimnames", lambda I, a, k: a[0])
     G.set("deriv", lambda I, a, k: (_ for _ in ()).throw(RError("deriv() of symbolic expressions is not supported by this front-end")))
     G.set("c_header", lambda I, a, k: NULL)

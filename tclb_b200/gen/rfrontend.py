@@ -226,8 +226,38 @@ def load_dynamics_r(model_dir: str, name: Optional[str] = None, options: Optiona
         return NULL
     env.set("AddStage", add_stage)
     I.source_hooks["conf.R"] = lambda I_, e: NULL
+    from . import rlib
+    rlib.install(I)
     path = os.path.join(model_dir, "Dynamics.R")
     I.run(open(path).read(), env)
     if finalize:
         m.finalize()
     return m, I
+
+
+def load_model(model_dir: str, name: Optional[str] = None, options: Optional[Dict[str, bool]] = None,
+               tclb_root: Optional[str] = None) -> ModelDef:
+    """A complete ModelDef (tables + node code) from an unmodified TCLB model directory: ``Dynamics.R`` through the
+    R-subset interpreter, ``Dynamics.c.Rt`` through the template engine (or ``Dynamics.c`` as it is).
+
+    `tclb_root` is the root of the source tree the model lives in (needed only for ``<?RT models/... ?>`` includes
+    that name files relative to it); by default it is guessed from `model_dir`."""
+    from . import poly, rtemplate
+    model_dir = os.path.abspath(model_dir)
+    if tclb_root is None:
+        p = model_dir
+        while p != os.path.dirname(p):
+            if os.path.isdir(os.path.join(p, "models")) and os.path.isdir(os.path.join(p, "src")):
+                tclb_root = p
+                break
+            p = os.path.dirname(p)
+    poly._tmp_counter[0] = 0
+    m, I = load_dynamics_r(model_dir, name=name, options=options, reference_src=None, finalize=False)
+    search = [model_dir] + ([tclb_root, os.path.join(tclb_root, "src")] if tclb_root else [])
+    rt = os.path.join(model_dir, "Dynamics.c.Rt")
+    if os.path.exists(rt):
+        m.code = rtemplate.render(I, I.globals, rt, search)
+    else:
+        m.code = rtemplate._read(os.path.join(model_dir, "Dynamics.c"))
+    m.finalize()
+    return m

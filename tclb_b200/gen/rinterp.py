@@ -283,6 +283,8 @@ class Interp:
         from .poly import Poly, PVec
         if isinstance(v, (Poly, PVec)):
             return -v
+        if isinstance(v, DataFrame):
+            return DataFrame(OrderedDict((k, [-x for x in c]) for k, c in v.cols.items()))
         return -_num(v)
 
     def eval_index_args(self, args, env):
@@ -379,7 +381,10 @@ class Interp:
 
     def source(self, name, env):
         base = os.path.basename(name)
-        if base in self.source_hooks:
+        key = name[2:] if name.startswith("./") else name
+        if key in self.source_hooks:
+            return self.source_hooks[key](self, self.globals)
+        if base == key and base in self.source_hooks:
             return self.source_hooks[base](self, env)
         p = self.find_file(name)
         if p is None:
@@ -395,6 +400,12 @@ class Interp:
         if op == "||":
             return vec(truthy(self.eval(ln, env)) or truthy(self.eval(rn, env)))
         a, b = self.eval(ln, env), self.eval(rn, env)
+        if isinstance(a, DataFrame) and op != "%in%":      # arithmetic on a data frame works on its matrix of values
+            a = np.array([list(c) for c in a.cols.values()], dtype=object).T
+            a = _num(a) if all(not isinstance(v, str) for v in a.ravel()) else a
+        if isinstance(b, DataFrame) and op != "%in%":
+            b = np.array([list(c) for c in b.cols.values()], dtype=object).T
+            b = _num(b) if all(not isinstance(v, str) for v in b.ravel()) else b
         if isinstance(a, (Poly, PVec)) or isinstance(b, (Poly, PVec)):
             return self.poly_binop(op, a, b)
         if op == "%in%":
@@ -624,6 +635,13 @@ class Interp:
             return x[cand[0]] if len(cand) == 1 else NULL
         if hasattr(x, "r_dollar"):
             return x.r_dollar(name)
+        from .poly import Poly
+        if isinstance(x, Poly):
+            # polyAlgebra keeps a polynomial as a table: one column of exponents per symbol plus the coefficients `.M`
+            terms = sorted(x.t.items(), key=lambda kv: (len(kv[0]), kv[0]))
+            if name == ".M":
+                return np.array([float(c) for _, c in terms], dtype=float)
+            return np.array([float(dict(m).get(name, 0)) for m, _ in terms], dtype=float)
         if x is NULL:
             return NULL
         raise RError(f"$ operator is invalid for this value (field {name})")
@@ -643,7 +661,7 @@ class Interp:
             new = self.replace(target, cur, val, env)
             self.assign(base, new, env, superassign)
             return
-        raise RError("invalid assignment target")
+        raise RError(f"invalid assignment target ({k}: {str(target)[:120]})")
 
     def _exists(self, node, env):
         try:

@@ -381,9 +381,9 @@ class Parser:
             return ("const", vec(_unescape(v)))
         if k == "id":
             v = v.strip("`")
-            if v in ("TRUE", "T"):
+            if v == "TRUE":
                 return ("const", vec(True))
-            if v in ("FALSE", "F"):
+            if v == "FALSE":
                 return ("const", vec(False))
             if v == "NULL":
                 return ("const", NULL)
