@@ -290,6 +290,7 @@ void Lattice::fill_launch(tclb_launch_t &L) const {
     L.stream = stream;
     L.nx = nx; L.ny = ny; L.nz = nz; L.gy = gy; L.gz = gz;
     L.off_x = region.x0; L.off_y = region.y0; L.off_z = region.z0;
+    L.pos_x = origin[0] + 0.5; L.pos_y = origin[1] + 0.5; L.pos_z = origin[2] + 0.5;
     L.tot_nx = tot[0]; L.tot_ny = tot[1]; L.tot_nz = tot[2];
     L.flags = flags_;
     L.cuts = cuts_dev_;

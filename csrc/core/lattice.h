@@ -69,6 +69,7 @@ class Lattice {
     HaloTarget halo[TCLB_MAX_NEIGH];
     void *stream;                  // cudaStream_t
     int block_x = 0, block_y = 0;
+    double origin[3] = {0.0, 0.0, 0.0};   // <Geometry px py pz>: node (i,j,k) sits at origin + (i,j,k) + 0.5
 
     // ---- memory access ----
     std::vector<PeerInfo> peers;   // indexed by rank (self included)

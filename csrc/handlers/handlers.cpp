@@ -203,6 +203,7 @@ class AcGeometry : public Action {
             catch (...) { node->parent->remove(tmp); throw; }
             node->parent->remove(tmp);
             Lattice *l = solver->domain->lat[r];
+            l->origin[0] = solver->px; l->origin[1] = solver->py; l->origin[2] = solver->pz;
             Box b; b.nx = l->nx; b.ny = l->ny; b.nz = l->nz;
             l->flag_overwrite(g->geom.data(), b);
             if (!g->Q.empty()) l->cuts_overwrite(g->Q.data());

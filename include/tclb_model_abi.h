@@ -12,7 +12,7 @@
 extern "C" {
 #endif
 
-#define TCLB_ABI_VERSION 6
+#define TCLB_ABI_VERSION 7
 #define TCLB_MAX_NEIGH 9            /* (dy,dz) in {-1,0,1}^2 ; x is never decomposed */
 #define TCLB_MAX_RANKS 16           /* subdomains that exchange Globals through peer memory (one box) */
 #define TCLB_GL_RING 8              /* depth of the Globals publication ring */
@@ -49,6 +49,7 @@ typedef struct {
     int nx, ny, nz;                     /* local interior extent (nx already padded) */
     int gy, gz;                         /* ghost thickness in y and z */
     int off_x, off_y, off_z;            /* position of the local block in the global lattice */
+    double pos_x, pos_y, pos_z;         /* coordinate of the centre of global node (0,0,0): origin + 0.5 (reference src/Lattice.cu.Rt:66-71) */
     int tot_nx, tot_ny, tot_nz;         /* global lattice extent */
     void *snap_in, *snap_out;           /* real_t[n_fields][nz+2gz][ny+2gy][nx] */
     const void *flags;                  /* flag_t[nz+2gz][ny+2gy][nx] */

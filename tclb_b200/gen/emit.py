@@ -77,6 +77,36 @@ def _fmt_default(v) -> str:
     return str(v)
 
 
+def _lattice_tables(code: str) -> str:
+    """Velocity/weight tables that model code may index at run time (the reference keeps them in constant memory,
+    src/Global.h.Rt:173-213): emitted only when the code names them, as a __constant__ copy for the device pass and a
+    plain array for the host pass of the same __host__ __device__ node code."""
+    import numpy as np
+    from .lbmlib import lattice_weights
+    from .rlib import velocity_sets
+    sets = velocity_sets()
+    tabs = {}
+    d2q9, d3q27 = sets["d2q9"], sets["d3q27"]
+    tabs["wf"] = lattice_weights(d2q9[:, :2])
+    tabs["wt"] = np.array([2 / 6] + [1 / 6] * 4)
+    tabs["d2q9_ex"], tabs["d2q9_ey"] = d2q9[:, 0], d2q9[:, 1]
+    tabs["d2q5_ex"], tabs["d2q5_ey"] = d2q9[:5, 0], d2q9[:5, 1]
+    w27 = lattice_weights(d3q27)
+    tabs["wg"] = w27
+    tabs["wtConv"] = np.array(sorted(w27.tolist(), key=lambda w: -w))       # rest, axes, edges, corners
+    tabs["wh"] = np.array([2 / 9] + [1 / 9] * 6 + [1 / 72] * 8)
+    tabs["d3q27_ex"], tabs["d3q27_ey"], tabs["d3q27_ez"] = d3q27[:, 0], d3q27[:, 1], d3q27[:, 2]
+    out = []
+    for name, v in tabs.items():
+        if re.search(r"(?<![\w.])" + name + r"\s*\[", code) is None:
+            continue
+        vals = ", ".join(repr(float(x)) for x in v)
+        out.append(f"#ifdef __CUDACC__\nstatic __constant__ real_t {name}_dev_[{len(v)}] = {{{vals}}};\n#endif\n"
+                   f"static const real_t {name}_host_[{len(v)}] = {{{vals}}};\n"
+                   f"#ifdef __CUDA_ARCH__\n#define {name} {name}_dev_\n#else\n#define {name} {name}_host_\n#endif")
+    return "\n".join(out)
+
+
 def emit_model_source(m: ModelDef, libname: str) -> str:
     """Return the text of the generated .cu file (precision chosen by -DTCLB_DOUBLE)."""
     m.finalize()
@@ -131,6 +161,7 @@ struct KArgs {
     int nx, ny, nz, NY, NZ;
     long long fstride;
     int off_x, off_y, off_z, tot_nx, tot_ny, tot_nz;
+    real_t pos_x, pos_y, pos_z;
     const real_t *in;
     real_t *out;
     // per-density source pointers, already shifted by the pull offset in y/z (x is handled by the wrapped
@@ -170,7 +201,9 @@ struct KArgs {
     macros: List[tuple] = []
     def M(name, body):
         macros.append((name, body))
-    M("X", "(n_x + ka_.off_x)"); M("Y", "(n_y + ka_.off_y)"); M("Z", "(n_z + ka_.off_z)")
+    # cell-centred real coordinates, like the reference's getX() (src/LatticeAccess.inc.cpp.Rt:274, src/Lattice.cu.Rt:66-71)
+    M("X", "((real_t)(n_x + ka_.off_x) + ka_.pos_x)"); M("Y", "((real_t)(n_y + ka_.off_y) + ka_.pos_y)")
+    M("Z", "((real_t)(n_z + ka_.off_z) + ka_.pos_z)")
     M("NodeType", "n_type")
     M("Time", "(ka_.iter)")
     M("average_iter", "(ka_.iter - ka_.reset_iter)")
@@ -205,6 +238,7 @@ struct KArgs {
                     qn += 1
     for name, body in macros:
         A(f"#define {name} {body}")
+    A(_lattice_tables(m.code))
 
     members = _member_decls([d.name for d in m.densities] + [f.name for f in m.fields])
     A(r"""

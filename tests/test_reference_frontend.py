@@ -51,3 +51,22 @@ def test_native_library_matches_reference_tables(reference_dir):
         assert np.array_equal(np.asarray(I.globals.get(name)).astype(int), sets[name]), name
     for name in ("d2q9", "d3q7", "d3q19"):
         assert rlib.known_matrix(sets[name]) is not None
+
+
+@pytest.mark.parametrize("ranks", [1, 2])
+def test_reference_pf_velocity_files_reproduce_drop_wall_golden(reference_dir, tclb_bin, tmp_path, ranks):
+    """tests/external/d3q27_pf_velocity/drop_wall_120_{1,2}cpu.test: the two-lattice phase-field model (6 stages per
+    Init, 4 per Iteration, dynamic stencil reads, 291 log columns) from the reference's own model files"""
+    from tclb_b200 import build
+    from tclb_b200.gen import rfrontend
+    m = rfrontend.load_model(os.path.join(reference_dir, "models/multiphase/d3q27_pf_velocity"), name="d3q27_pf_velocity")
+    build.build_custom(m, "ref_d3q27_pf_velocity", "double")
+    case = os.path.join(reference_dir, "tests/external/d3q27_pf_velocity")
+    (tmp_path / "drop_wall_120.xml").write_text(open(os.path.join(case, "drop_wall_120.xml")).read())
+    r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", "--ranks", str(ranks), "ref_d3q27_pf_velocity", "drop_wall_120.xml"],
+                       cwd=tmp_path, capture_output=True, text=True, timeout=1200)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    d = subprocess.run(["python", os.path.join(root, "tools", "csvdiff"), "-a", str(tmp_path / "output" / "drop_wall_120_Log_P00_00000000.csv"),
+                        "-b", os.path.join(case, "output", "drop_wall_120_Log_P00_00000000.csv"), "-x", "1e-8"], capture_output=True, text=True)
+    assert d.returncode == 0, d.stdout
