@@ -196,6 +196,40 @@ def all_variants() -> List[str]:
     return out
 
 
+def build_from_dir(model_dir: str, name: Optional[str] = None, precision: str = "float", options: Optional[dict] = None,
+                   libname: Optional[str] = None) -> Path:
+    """Build a model library straight from an unmodified TCLB model directory (Dynamics.R + Dynamics.c[.Rt] + conf.mk):
+    the R-subset interpreter and the template engine lower it, the generator emits the fused sm_100a kernels.
+    The library is named ``ref_<model>[_<option>...]`` unless `libname` is given."""
+    from .gen import rfrontend
+    with _GEN_LOCK:
+        m = rfrontend.load_model(model_dir, name=name, options=options)
+    on = [k for k, v in (options or {}).items() if v]
+    lib = libname or "ref_" + "_".join([m.name] + on)
+    return build_custom(m, lib, precision)
+
+
+# models of a mounted TCLB tree that are built next to the native ones when the tree is present
+REFERENCE_ROOT = Path(os.environ.get("TCLB_REFERENCE", "/root/reference"))
+REFERENCE_MODELS = ["multiphase/d3q27_pf_velocity", "flow/d2q9", "flow/d3q19", "flow/d3q27_cumulant", "heat/d3q19_heat",
+                    "electrokinetic/d2q9_poison_boltzmann", "electrokinetic/d2q9_npe_guo", "multiphase/d2q9_kuper"]
+
+
+def build_reference_models(precisions=("float", "double"), verbose=False) -> List[Path]:
+    out = []
+    if not (REFERENCE_ROOT / "models").is_dir():
+        return out
+    for rel in REFERENCE_MODELS:
+        d = REFERENCE_ROOT / "models" / rel
+        if not d.is_dir():
+            continue
+        for p in precisions:
+            out.append(build_from_dir(str(d), precision=p))
+            if verbose:
+                print(f"built {out[-1]}")
+    return out
+
+
 def build_all(models: Optional[List[str]] = None, precisions=("float", "double"), force=False, verbose=False, jobs=None) -> None:
     build_core(force=force, verbose=verbose)
     models = models or all_variants()
@@ -213,7 +247,15 @@ def main(argv=None) -> int:
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--list", action="store_true")
     ap.add_argument("--core-only", action="store_true")
+    ap.add_argument("--dir", action="append", default=[], help="build from an unmodified TCLB model directory (repeatable)")
+    ap.add_argument("--option", action="append", default=[], help="model option to switch on for --dir builds (repeatable)")
     a = ap.parse_args(argv)
+    if a.dir:
+        build_core(force=a.force, verbose=True)
+        for d in a.dir:
+            for pr in (("float", "double") if a.precision == "both" else (a.precision,)):
+                print(build_from_dir(d, precision=pr, options={o: True for o in a.option}))
+        return 0
     if a.list:
         print("\n".join(all_variants()))
         return 0

@@ -263,7 +263,8 @@ struct Node {
             A(f"    real_t {s.name};")
     for s in m.settings:
         A(f"    const real_t &{s.name};")
-    init_refs = "".join(f", {s.name}(a_.settings[{i}])" for i, s in enumerate(m.settings))
+    # brace initialisers: a field of the same name is a function-like macro and would swallow `name(`
+    init_refs = "".join(f", {s.name}{{a_.settings[{i}]}}" for i, s in enumerate(m.settings))
     A("    TCLB_HD Node(const KArgs &a_, int x, int y, int z, real_t *gacc = nullptr) : ka_(a_), n_x(x), n_y(y), n_z(z), gacc_(gacc)" + init_refs + " {")
     A(r"""
         n_idx = ((z + GZ) * ka_.NY + (y + GY)) * ka_.nx + x;

@@ -154,3 +154,34 @@ def test_gpu_globals_reproducible_and_objective_weights():
     got = d.globals()
     for k in ("Mass", "XMomentum", "Flux"):
         assert abs(got[k] - ref[k]) <= 2e-4 * max(1.0, abs(ref[k])) + 2e-7 * float(np.prod(shape)), (k, got[k], ref[k])
+
+
+def test_gpu_reference_pf_velocity_matches_cpu_oracle(tclb_bin, tmp_path):
+    """d3q27_pf_velocity lowered from the reference's model files (library built when the reference tree is mounted):
+    the fused multi-stage GPU kernels against the CPU restatement of the same generated code, through the case runner"""
+    import csv
+    import shutil
+    import subprocess
+    lib = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tclb_b200", "_lib", "libtclb_ref_d3q27_pf_velocity_double.so")
+    if not os.path.exists(lib):
+        pytest.skip("ref_d3q27_pf_velocity was not built (no reference tree at build time)")
+    case = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cases", "pf_drop_on_wall.xml")
+    logs = {}
+    for backend in ("cpu", "gpu"):
+        wd = tmp_path / backend
+        wd.mkdir()
+        shutil.copy(case, wd / "case.xml")
+        r = subprocess.run([tclb_bin, f"--{backend}", "--precision", "double", "ref_d3q27_pf_velocity", "case.xml"], cwd=wd,
+                           capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        logs[backend] = list(csv.reader(open(wd / "output" / "case_Log_P00_00000000.csv")))
+    hdr = logs["cpu"][0]
+    assert hdr == logs["gpu"][0] and len(logs["cpu"]) == len(logs["gpu"]) == 7
+    for a, b in zip(logs["cpu"][1:], logs["gpu"][1:]):
+        for n, x, y in zip(hdr, a, b):
+            if n == "Walltime":
+                continue
+            x, y = float(x), float(y)
+            assert abs(x - y) <= 1e-9 * max(abs(x), abs(y)) + 1e-11, (n, x, y)
+    liq = [float(r[hdr.index("LiqTotalPhase")]) for r in logs["gpu"][1:]]
+    assert liq[0] > 100 and abs(liq[-1] - liq[0]) < 0.05 * liq[0]
