@@ -298,6 +298,13 @@ int tclb_solver_run(tclb_solver_h *h) {
     if (h->s->run() != 0) fail("case run failed (see log)");
     GUARD_END_INT
 }
+int tclb_solver_set_script_hook(tclb_solver_h *h, tclb_script_fn fn, void *user) {
+    GUARD_BEGIN h->s->script_hook = fn; h->s->script_user = user; GUARD_END_INT
+}
+int tclb_solver_zone_id(tclb_solver_h *h, const char *name) {
+    auto it = h->s->setting_zones.find(name);
+    return it == h->s->setting_zones.end() ? -1 : it->second;
+}
 tclb_domain_h *tclb_solver_domain(tclb_solver_h *h) { return h->dom.d ? &h->dom : nullptr; }
 int tclb_solver_iter(tclb_solver_h *h) { return h->s->iter; }
 const char *tclb_solver_outpath(tclb_solver_h *h) { return h->s->outpath.c_str(); }

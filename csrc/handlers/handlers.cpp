@@ -833,6 +833,39 @@ TCLB_REGISTER_HANDLER("SaveBinary", CbSaveBinary)
 class CbSaveMemoryDump : public CbSaveBinary {};
 TCLB_REGISTER_HANDLER("SaveMemoryDump", CbSaveMemoryDump)
 
+// <RunPython> / <RunR> (reference src/Handlers/cbRunR.cpp): the code runs inside the embedding Python process through
+// the script hook (tclb_solver_set_script_hook; tclb_b200.runtime.Solver installs one that exposes the same object
+// surface: Solver.Settings/Fields/Quantities/Globals/Geometry/Actions/Info).  Without a hook (plain bin/tclb) the
+// element fails with a message that says how to run the case instead.
+class CbRunScript : public Callback {
+  public:
+    std::string code;
+    int init() override {
+        Callback::init();
+        if (node->has_attr("file")) {
+            FILE *f = fopen(node->attr("file").c_str(), "rb");
+            if (!f) { logf(L_ERROR, "<%s>: cannot open %s", node->name.c_str(), node->attr("file").c_str()); return -1; }
+            char buf[4096]; size_t n;
+            while ((n = fread(buf, 1, sizeof(buf), f)) > 0) code.append(buf, n);
+            fclose(f);
+        } else code = node->text();
+        if (!solver->script_hook) {
+            logf(L_ERROR, "<%s> needs the Python coupling: run the case with `python -m tclb_b200.run <model> <case.xml>`", node->name.c_str());
+            return -1;
+        }
+        return 0;                                     // without Iterations= the container runs do_it() once, now
+    }
+    int do_it() override {
+        for (int r : solver->domain->local) solver->domain->lat[r]->sync();
+        int rc = solver->script_hook(solver->script_user, node->name.c_str(), code.c_str(), solver->iter);
+        if (rc != 0) { logf(L_ERROR, "<%s> script failed", node->name.c_str()); return -1; }
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("RunPython", CbRunScript)
+class CbRunR : public CbRunScript {};
+TCLB_REGISTER_HANDLER("RunR", CbRunR)
+
 // elements whose back-ends are not available in this build: recognised, fail with a clear message
 // (the reference does the same in its #else branches, e.g. src/Handlers/cbHDF5.cpp:129-132)
 class Unavailable : public Handler {

@@ -67,6 +67,10 @@ class Solver {
     std::vector<double> log_scales;
     double px = 0, py = 0, pz = 0;
     bool stop_requested = false;
+    // in-process scripting hook (<RunPython>/<RunR>): set by the embedding program, called with the element name, the
+    // code (text of the element or of its file= attribute) and the iteration; a non-zero return aborts the run
+    int (*script_hook)(void *user, const char *element, const char *code, int iteration) = nullptr;
+    void *script_user = nullptr;
 
     // ---- set-up ----
     void load_case(const std::string &file, const std::vector<std::string> &xpath_args);

@@ -115,8 +115,12 @@ void tclb_solver_destroy(tclb_solver_h *);
 int tclb_solver_load_file(tclb_solver_h *, const char *case_xml, const char *const *xpath_args, int n_args);
 int tclb_solver_load_string(tclb_solver_h *, const char *xml_text, const char *case_name, const char *const *xpath_args, int n_args);
 int tclb_solver_run(tclb_solver_h *);
+/* <RunPython>/<RunR> elements call this hook (element name, code text, iteration); non-zero return aborts the run */
+typedef int (*tclb_script_fn)(void *user, const char *element, const char *code, int iteration);
+int tclb_solver_set_script_hook(tclb_solver_h *, tclb_script_fn fn, void *user);
 tclb_domain_h *tclb_solver_domain(tclb_solver_h *);     /* borrowed handle, valid while the solver lives */
 int tclb_solver_iter(tclb_solver_h *);
+int tclb_solver_zone_id(tclb_solver_h *, const char *zone_name);     /* setting-zone id of a named zone, -1 if unknown */
 const char *tclb_solver_outpath(tclb_solver_h *);
 
 #ifdef __cplusplus

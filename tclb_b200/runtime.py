@@ -256,9 +256,25 @@ class Domain:
                     from .utils.units import UnitEnv
                     self.set_setting(n, UnitEnv().alt(v))
 
+    @classmethod
+    def from_handle(cls, model: Model, handle, nranks: int, local_ranks: Sequence[int]) -> "Domain":
+        """wrap a lattice owned by a native Solver (borrowed handle: never destroyed from here)"""
+        self = cls.__new__(cls)
+        self.lib, self.model, self.h, self._borrowed = core(), model, handle, True
+        self.backend = None
+        self.nranks, self.local = nranks, list(local_ranks)
+        divy, divz = C.c_int(), C.c_int()
+        boxes = (C.c_int * (6 * nranks))()
+        _check(self.lib.tclb_domain_decomposition(self.h, C.byref(divy), C.byref(divz), boxes))
+        self.divy, self.divz = divy.value, divz.value
+        self.boxes = [tuple(boxes[6 * r:6 * r + 6]) for r in range(nranks)]
+        self.shape = (max(b[0] + b[3] for b in self.boxes), max(b[1] + b[4] for b in self.boxes), max(b[2] + b[5] for b in self.boxes))
+        return self
+
     def close(self):
         if getattr(self, "h", None):
-            self.lib.tclb_domain_destroy(self.h)
+            if not getattr(self, "_borrowed", False):
+                self.lib.tclb_domain_destroy(self.h)
             self.h = None
 
     def __del__(self):
