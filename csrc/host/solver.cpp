@@ -141,6 +141,19 @@ void Solver::set_size(int nx, int ny, int nz) {
         const Box &b = domain->dec.boxes[r];
         logf(L_OUTPUT, "Local lattice size (rank %d): %dx%dx%d", r, b.nx, b.ny, b.nz);
     }
+    // launch-shape table of every kernel (reference src/GetThreads.cpp:7-45 prints the same at start-up)
+    if (opt.backend == TCLB_BACKEND_CUDA && model->d->kernel_info) {
+        logf(L_NOTICE, "  Threads  |      Action");
+        for (int s = 0; s < model->d->n_stages; s++)
+            for (int g = 0; g < 4; g++) {
+                int regs = 0, smem = 0, lmem = 0, maxthr = 0;
+                if (model->d->kernel_info(s, g, &regs, &smem, &lmem, &maxthr) != 0) continue;
+                static const char *gm[] = {"NoGlobals", "IntegrateGlobals", "OnlyObjective", "Globals+Objective"};
+                const int lnx = domain->lat[domain->local[0]]->nx, bx = lnx >= 128 ? 128 : (lnx >= 64 ? 64 : 32);
+                logf(L_NOTICE, "  %3dx%-3d  | %s<%s>  regs %d, shared %d B, local %d B, max %d threads", bx, 128 / bx,
+                     model->d->stages[s].name, gm[g], regs, smem, lmem, maxthr);
+            }
+    }
     // defaults (unit-aware strings)
     for (int i = 0; i < model->d->n_zonesettings; i++) domain->set_zone_setting(i, -1, units.alt(model->d->zonesettings[i].default_value));
     for (int i = 0; i < model->d->n_settings; i++)

@@ -70,3 +70,14 @@ def test_reference_pf_velocity_files_reproduce_drop_wall_golden(reference_dir, t
     d = subprocess.run(["python", os.path.join(root, "tools", "csvdiff"), "-a", str(tmp_path / "output" / "drop_wall_120_Log_P00_00000000.csv"),
                         "-b", os.path.join(case, "output", "drop_wall_120_Log_P00_00000000.csv"), "-x", "1e-8"], capture_output=True, text=True)
     assert d.returncode == 0, d.stdout
+
+
+def test_reference_test_suite_files_pass_with_the_runner(reference_dir, tclb_bin):
+    """tools/run_tests.py executes the reference's own `.test` scripts (karman, 2 ranks, restart, restart on 2 ranks,
+    expected failure) against the native d2q9 model"""
+    from tclb_b200 import build
+    build.build_model_lib("d2q9", "double")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run(["python", os.path.join(root, "tools", "run_tests.py"), "d2q9", os.path.join(reference_dir, "tests/external/d2q9")],
+                       capture_output=True, text=True, timeout=1800)
+    assert r.returncode == 0 and "5 of 5 tests passed" in r.stdout, r.stdout[-3000:]
