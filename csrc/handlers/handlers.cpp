@@ -513,6 +513,33 @@ class CbVTK : public Callback {
 };
 TCLB_REGISTER_HANDLER("VTK", CbVTK)
 
+// <HDF5 name what compress write_xdmf point_data precision dx..nz> (reference cbHDF5.cpp): one .h5 for the whole output
+// region + an .xmf index.  `compress` and `chunk` are accepted and ignored (the built-in writer stores contiguous data).
+class CbHDF5 : public Callback {
+    std::string nm;
+    NameSet what;
+    Box reg;
+    bool xdmf = true, point = false, dbl = false;
+  public:
+    int init() override {
+        Callback::init();
+        nm = node->attr("name", "HDF5");
+        what.add_from_string(node->attr("what", "all"));
+        reg = region_from_attrs(this, solver->total);
+        if (reg.size() == 0) { logf(L_FATAL, "HDF5 \"%s\" output has size 0", nm.c_str()); return -1; }
+        if (node->has_attr("write_xdmf")) xdmf = node->attr_bool("write_xdmf");
+        point = node->attr_bool("point_data");
+        std::string pr = node->attr("precision", "");
+        if (pr == "double") dbl = true;
+        else if (pr == "float" || pr.empty()) dbl = false;
+        else { logf(L_ERROR, "HDF5: precision should be float or double"); return -1; }
+        if (node->has_attr("compress") && node->attr_bool("compress")) logf(L_WARNING, "HDF5: compress is ignored, the data are stored contiguously");
+        return 0;
+    }
+    int do_it() override { return solver->write_hdf5(nm, what, reg, dbl, xdmf, point); }
+};
+TCLB_REGISTER_HANDLER("HDF5", CbHDF5)
+
 class CbTXT : public Callback {
     std::string nm;
     NameSet what;

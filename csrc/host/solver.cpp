@@ -1,4 +1,5 @@
 #include "solver.h"
+#include "../io/h5min.h"
 #include "../core/common.h"
 #include "../handlers/handler.h"
 #include "../io/vtk.h"
@@ -271,6 +272,95 @@ int Solver::write_vtk(const std::string &name, const NameSet &what, const Box &r
         }
         vtk.finish();
         vtk.close();
+    }
+    return 0;
+}
+
+// <HDF5>: one file for the whole output region (reference src/hdf5Lattice.cpp:26-339: datasets [nz][ny][nx] or
+// [nz][ny][nx][3], one per node-type group and quantity, values in SI units; .xmf = 3DCoRectMesh index)
+int Solver::write_hdf5(const std::string &name, const NameSet &what, const Box &region_out, bool as_double, bool write_xdmf, bool point_data) {
+    logf(L_OUTPUT, "%8d it writing hdf5", iter);
+    const tclb_model_t *d = model->d;
+    for (int r = 0; r < opt.nranks; r++)
+        if (!domain->lat[r]) fail("<HDF5> needs every subdomain in this process (run the ranks in one process)");
+    const size_t N = (size_t)region_out.size();
+    H5MinWriter h5;
+    std::string xattr;
+    const std::string file = out_iter_collective_file(name, ".h5");
+    const std::string base = file.substr(file.find_last_of('/') == std::string::npos ? 0 : file.find_last_of('/') + 1);
+    const std::string dims3 = strf("%d %d %d", region_out.nz, region_out.ny, region_out.nx);
+    auto xdmf_attr = [&](const char *fname, int comp, int prec, const char *type) {
+        xattr += strf("      <Attribute Center=\"%s\" %sName=\"%s\">\n        <DataItem DataType=\"%s\" Dimensions=\"%s%s\" Format=\"HDF\" Precision=\"%d\">%s:/%s</DataItem>\n      </Attribute>\n",
+                      point_data ? "Node" : "Cell", comp == 3 ? "AttributeType=\"Vector\" " : "", fname, type, dims3.c_str(), comp == 3 ? " 3" : "", prec, base.c_str(), fname);
+    };
+    // flags of the whole region
+    std::vector<uint32_t> flags(N);
+    auto scatter = [&](int r, const Box &reg, auto &&put) {
+        for (int k = 0; k < reg.nz; k++)
+            for (int j = 0; j < reg.ny; j++)
+                for (int i = 0; i < reg.nx; i++) {
+                    size_t src = ((size_t)k * reg.ny + j) * reg.nx + i;
+                    size_t dst = ((size_t)(k + reg.z0 - region_out.z0) * region_out.ny + (j + reg.y0 - region_out.y0)) * region_out.nx + (i + reg.x0 - region_out.x0);
+                    put(src, dst);
+                }
+        (void)r;
+    };
+    for (int r = 0; r < opt.nranks; r++) {
+        Lattice *l = domain->lat[r];
+        Box reg = domain->dec.boxes[r].intersect(region_out);
+        if (reg.empty()) continue;
+        Box loc = reg; loc.x0 -= l->region.x0; loc.y0 -= l->region.y0; loc.z0 -= l->region.z0;
+        std::vector<uint32_t> fl((size_t)reg.size());
+        l->get_flags(loc, fl.data());
+        scatter(r, reg, [&](size_t s, size_t t) { flags[t] = fl[s]; });
+    }
+    std::vector<unsigned char> small(N);
+    for (int g = 0; g < d->n_nodegroups; g++) {
+        const tclb_nodegroup_t &G = d->nodegroups[g];
+        if (!((what.all && G.save) || what.explicitly_in(G.name))) continue;
+        for (size_t i = 0; i < N; i++) small[i] = (unsigned char)((flags[i] & G.mask) >> G.shift);
+        h5.add(G.name, H5MinWriter::U8, {(uint64_t)region_out.nz, (uint64_t)region_out.ny, (uint64_t)region_out.nx}, small.data());
+        xdmf_attr(G.name, 1, 1, "UChar");
+    }
+    for (int q = 0; q < d->n_quantities; q++) {
+        if (!what.in(d->quantities[q].name)) continue;
+        const double v = units.alt(d->quantities[q].unit);
+        const int comp = d->quantities[q].vector ? 3 : 1;
+        std::vector<double> full(N * comp);
+        for (int r = 0; r < opt.nranks; r++) {
+            Lattice *l = domain->lat[r];
+            Box reg = domain->dec.boxes[r].intersect(region_out);
+            if (reg.empty()) continue;
+            Box loc = reg; loc.x0 -= l->region.x0; loc.y0 -= l->region.y0; loc.z0 -= l->region.z0;
+            std::vector<char> tmp((size_t)reg.size() * comp * model->real_size());
+            l->get_quantity(q, loc, tmp.data(), 1 / v);
+            scatter(r, reg, [&](size_t s, size_t t) {
+                for (int c = 0; c < comp; c++)
+                    full[t * comp + c] = model->real_size() == 8 ? ((const double *)tmp.data())[s * comp + c] : (double)((const float *)tmp.data())[s * comp + c];
+            });
+        }
+        std::vector<uint64_t> dims = {(uint64_t)region_out.nz, (uint64_t)region_out.ny, (uint64_t)region_out.nx};
+        if (comp == 3) dims.push_back(3);
+        if (as_double) h5.add(d->quantities[q].name, H5MinWriter::F64, dims, full.data());
+        else { std::vector<float> f32(full.begin(), full.end()); h5.add(d->quantities[q].name, H5MinWriter::F32, dims, f32.data()); }
+        xdmf_attr(d->quantities[q].name, comp, as_double ? 8 : 4, "Float");
+    }
+    h5.write(file);
+    if (write_xdmf) {
+        const double m = units.alt("1m"), sec = units.alt("1s"), shift = point_data ? 0.5 : 0.0;
+        const std::string xf = out_iter_collective_file(name, ".xmf");
+        FILE *f = fopen(xf.c_str(), "w");
+        if (!f) fail("cannot write %s", xf.c_str());
+        fprintf(f, "<?xml version=\"1.0\"?>\n<Xdmf xmlns:xi=\"http://www.w3.org/2001/XInclude\" Version=\"3.0\">\n  <Domain>\n    <Grid Name=\"Lattice\">\n");
+        fprintf(f, "      <Time Value=\"%.15g\"/>\n", iter / sec);
+        fprintf(f, "      <Geometry Origin=\"\" Type=\"ORIGIN_DXDYDZ\">\n        <DataItem DataType=\"Float\" Dimensions=\"3\" Format=\"XML\" Precision=\"8\">%.15g %.15g %.15g</DataItem>\n",
+                (pz + shift + region_out.z0) / m, (py + shift + region_out.y0) / m, (px + shift + region_out.x0) / m);
+        fprintf(f, "        <DataItem DataType=\"Float\" Dimensions=\"3\" Format=\"XML\" Precision=\"8\">%.15g %.15g %.15g</DataItem>\n      </Geometry>\n", 1 / m, 1 / m, 1 / m);
+        if (point_data) fprintf(f, "      <Topology Dimensions=\"%s\" Type=\"3DCoRectMesh\"/>\n", dims3.c_str());
+        else fprintf(f, "      <Topology Dimensions=\"%d %d %d\" Type=\"3DCoRectMesh\"/>\n", region_out.nz + 1, region_out.ny + 1, region_out.nx + 1);
+        fputs(xattr.c_str(), f);
+        fprintf(f, "    </Grid>\n  </Domain>\n</Xdmf>\n");
+        fclose(f);
     }
     return 0;
 }

@@ -31,6 +31,7 @@ ELEMENTS = {
     "Container": ("container", "", "grouping"),
     "EvalIf": ("container", "opt_present opt_missing", "children run only if the model has / lacks an option"),
     "VTK": ("callback", "Iterations name what dx dy dz nx ny nz", "ImageData pieces + .pvti index"),
+    "HDF5": ("callback", "Iterations name what compress write_xdmf point_data precision dx dy dz nx ny nz", "one .h5 for the output region + .xmf (3DCoRectMesh) index"),
     "TXT": ("callback", "Iterations name what gzip", "one text file per quantity"),
     "BIN": ("callback", "Iterations name", "raw binary per quantity"),
     "Log": ("callback", "Iterations name", "CSV log of settings, zone settings and Globals"),
