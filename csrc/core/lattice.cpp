@@ -32,7 +32,7 @@ Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &loca
     gy = m->d->gy; gz = m->d->gz;
     NY = ny + 2 * gy; NZ = nz + 2 * gz;
     plane_elems = (size_t)nx * NY * NZ;
-    snap_bytes = plane_elems * m->d->n_fields * m->real_size();
+    snap_bytes = plane_elems * m->d->n_fields * m->storage_size();
     int s0 = arena_.reserve(snap_bytes, "snapshot0");
     int s1 = arena_.reserve(snap_bytes, "snapshot1");
     int sf = arena_.reserve(plane_elems * m->flag_size(), "flags");
@@ -134,7 +134,7 @@ void *Lattice::scratch(size_t bytes) {
     return scratch_;
 }
 void *Lattice::field_ptr(int snap, int field) const {
-    return (char *)snap_[snap] + (size_t)field * plane_elems * model->real_size();
+    return (char *)snap_[snap] + (size_t)field * plane_elems * model->storage_size();
 }
 
 // ---- flags -------------------------------------------------------------------------------
@@ -180,8 +180,71 @@ void Lattice::cuts_overwrite(const uint16_t *cuts) {
 }
 
 // ---- fields ------------------------------------------------------------------------------
-void Lattice::copy_field_out(int field, void *dst) const {
-    const int rs = model->real_size();
+// IEEE binary16 <-> float on the host (the lattice may be stored narrower than the node code computes)
+static float half_to_float(uint16_t h) {
+    const uint32_t sign = (uint32_t)(h & 0x8000u) << 16, exp = (h >> 10) & 31u, man = h & 1023u;
+    uint32_t bits;
+    if (exp == 0) {
+        if (man == 0) bits = sign;
+        else {                                   // subnormal: renormalise
+            int e = -1; uint32_t m = man;
+            do { e++; m <<= 1; } while (!(m & 1024u));
+            bits = sign | (uint32_t)(127 - 15 - e) << 23 | (m & 1023u) << 13;
+        }
+    } else if (exp == 31) bits = sign | 0x7f800000u | man << 13;
+    else bits = sign | (exp + 127 - 15) << 23 | man << 13;
+    float f; memcpy(&f, &bits, 4); return f;
+}
+static uint16_t float_to_half(float f) {
+    uint32_t x; memcpy(&x, &f, 4);
+    const uint32_t sign = (x >> 16) & 0x8000u;
+    const int32_t exp = (int32_t)((x >> 23) & 255u) - 127 + 15;
+    uint32_t man = x & 0x7fffffu;
+    if (((x >> 23) & 255u) == 255u) return (uint16_t)(sign | 0x7c00u | (man ? 0x200u : 0));
+    if (exp >= 31) return (uint16_t)(sign | 0x7c00u);
+    if (exp <= 0) {
+        if (exp < -10) return (uint16_t)sign;
+        man |= 0x800000u;
+        const int shift = 14 - exp;
+        uint32_t h = man >> shift;
+        const uint32_t rem = man & ((1u << shift) - 1), half = 1u << (shift - 1);
+        if (rem > half || (rem == half && (h & 1))) h++;
+        return (uint16_t)(sign | h);
+    }
+    uint32_t h = (uint32_t)exp << 10 | man >> 13;
+    const uint32_t rem = man & 0x1fffu;
+    if (rem > 0x1000u || (rem == 0x1000u && (h & 1))) h++;       // round to nearest even (may carry into the exponent)
+    return (uint16_t)(sign | h);
+}
+// storage_t -> real_t (+ shift) and back, for the host-side field accessors
+void Lattice::storage_to_real(int field, const void *src, void *dst, size_t n) const {
+    const int rs = model->real_size(), ss = model->storage_size();
+    const double sh = model->field_shift(field);
+    for (size_t i = 0; i < n; i++) {
+        const double v = (ss == 2 ? (double)half_to_float(((const uint16_t *)src)[i]) : ss == 4 ? (double)((const float *)src)[i] : ((const double *)src)[i]) + sh;
+        if (rs == 4) ((float *)dst)[i] = (float)v; else ((double *)dst)[i] = v;
+    }
+}
+void Lattice::real_to_storage(int field, const void *src, void *dst, size_t n) const {
+    const int rs = model->real_size(), ss = model->storage_size();
+    const double sh = model->field_shift(field);
+    for (size_t i = 0; i < n; i++) {
+        const double v = (rs == 4 ? (double)((const float *)src)[i] : ((const double *)src)[i]) - sh;
+        if (ss == 2) ((uint16_t *)dst)[i] = float_to_half((float)v);
+        else if (ss == 4) ((float *)dst)[i] = (float)v;
+        else ((double *)dst)[i] = v;
+    }
+}
+void Lattice::copy_field_out(int field, void *dst_real) const {
+    const int rs = model->storage_size();
+    const bool convert = rs != model->real_size() || model->field_shift(field) != 0.0;
+    std::vector<char> staged(convert ? (size_t)nz * ny * nx * rs : 0);
+    void *dst = convert ? (void *)staged.data() : dst_real;
+    copy_field_out_raw(field, dst);
+    if (convert) storage_to_real(field, staged.data(), dst_real, (size_t)nz * ny * nx);
+}
+void Lattice::copy_field_out_raw(int field, void *dst) const {
+    const int rs = model->storage_size();
     const char *src = (const char *)field_ptr(cur, field);
     if (backend == TCLB_BACKEND_CUDA) {
         TCLB_CUDA(cudaSetDevice(device));
@@ -194,8 +257,16 @@ void Lattice::copy_field_out(int field, void *dst) const {
             memcpy((char *)dst + (size_t)z * ny * nx * rs, src + ((size_t)(z + gz) * NY + gy) * nx * rs, (size_t)ny * nx * rs);
     }
 }
-void Lattice::copy_field_in(int field, const void *srcv) {
-    const int rs = model->real_size();
+void Lattice::copy_field_in(int field, const void *src_real) {
+    const int ss = model->storage_size();
+    if (ss != model->real_size() || model->field_shift(field) != 0.0) {
+        std::vector<char> staged((size_t)nz * ny * nx * ss);
+        real_to_storage(field, src_real, staged.data(), (size_t)nz * ny * nx);
+        copy_field_in_raw(field, staged.data());
+    } else copy_field_in_raw(field, src_real);
+}
+void Lattice::copy_field_in_raw(int field, const void *srcv) {
+    const int rs = model->storage_size();
     char *dst = (char *)field_ptr(cur, field);
     if (backend == TCLB_BACKEND_CUDA) {
         TCLB_CUDA(cudaSetDevice(device));
@@ -577,7 +648,7 @@ void Domain::copy_exchange(int s) {
     // Baseline halo path: copy the border rows of every local rank into the ghost rows of its
     // neighbours with stream-ordered memcpys (plays the role of the reference's
     // D2H -> MPI_Isend/Irecv -> H2D, src/Lattice.cu.Rt:327-389, without the host bounce).
-    const int rs = model->real_size();
+    const int rs = model->storage_size();
     const int nf = model->d->n_fields;
     if (backend == TCLB_BACKEND_CUDA) sync();
     for (int r : local) {

@@ -88,6 +88,10 @@ class Lattice {
     void cuts_overwrite(const uint16_t *cuts_local26);     // [26][nz][ny][nx] or nullptr
     void copy_field_out(int field, void *dst_native) const;  // interior only, [nz][ny][nx] in real_t
     void copy_field_in(int field, const void *src_native);
+    void copy_field_out_raw(int field, void *dst_storage) const;   // same, in storage_t without the shift
+    void copy_field_in_raw(int field, const void *src_storage);
+    void storage_to_real(int field, const void *src, void *dst, size_t n) const;
+    void real_to_storage(int field, const void *src, void *dst, size_t n) const;
     void fill_field(int field, double v);
     void get_quantity(int q, const Box &local_box, void *dst_native, double scale, bool dst_on_device = false);
     void color(int zplane, float scale, unsigned char *rgba_host_or_dev, bool dst_on_device = false);

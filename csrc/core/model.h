@@ -17,6 +17,8 @@ class Model {
     std::string path;
     int real_size() const { return d->real_size; }
     int flag_size() const { return d->flag_size; }
+    int storage_size() const { return d->storage_size; }              // element size of a lattice value in memory
+    double field_shift(int f) const { return d->storage_shifted ? d->field_shift[f] : 0.0; }
     int find_setting(const std::string &n) const;
     int find_zonesetting(const std::string &n) const;
     int find_global(const std::string &n) const;
@@ -29,7 +31,7 @@ class Model {
     const tclb_nodegroup_t *find_nodegroup(const std::string &n) const;
     bool has_option(const std::string &n) const;
     // bytes moved per node update by the reference's accounting (src/main.cpp:127)
-    double bytes_per_update() const { return 2.0 * d->n_fields * d->real_size + d->flag_size; }
+    double bytes_per_update() const { return 2.0 * d->n_fields * d->storage_size + d->flag_size; }
   private:
     Model() : d(nullptr), handle(nullptr) {}
     void *handle;

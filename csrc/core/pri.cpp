@@ -37,7 +37,7 @@ size_t Lattice::pri_bytes() const {
     for (int m = 0; m < 27; m++)
         for (int k = 0; k < model->d->n_fields; k++)
             if (piece(*this, m, k, p)) tot += p.elems;
-    return tot * model->real_size();
+    return tot * model->storage_size();       // the image holds storage_t values, like the reference's checkpoints
 }
 
 template <class T, bool SAVE>
@@ -75,7 +75,8 @@ static void pri_transfer(const Lattice &L, T *slab, T *image) {
 void Lattice::save_pri(const std::string &file) const {
     std::vector<char> slab(snap_bytes), image(pri_bytes());
     to_host(slab.data(), snap_[cur], snap_bytes);
-    if (model->real_size() == 4) pri_transfer<float, true>(*this, (float *)slab.data(), (float *)image.data());
+    if (model->storage_size() == 2) pri_transfer<uint16_t, true>(*this, (uint16_t *)slab.data(), (uint16_t *)image.data());
+    else if (model->storage_size() == 4) pri_transfer<float, true>(*this, (float *)slab.data(), (float *)image.data());
     else pri_transfer<double, true>(*this, (double *)slab.data(), (double *)image.data());
     make_parent_dirs(file);
     FILE *f = fopen(file.c_str(), "wb");
@@ -96,7 +97,8 @@ void Lattice::load_pri(const std::string &file) {
         fail("%s: size mismatch (expected %zu bytes): the file was written for another model, precision, lattice size or decomposition",
              file.c_str(), image.size());
     to_host(slab.data(), snap_[cur], snap_bytes);
-    if (model->real_size() == 4) pri_transfer<float, false>(*this, (float *)slab.data(), (float *)image.data());
+    if (model->storage_size() == 2) pri_transfer<uint16_t, false>(*this, (uint16_t *)slab.data(), (uint16_t *)image.data());
+    else if (model->storage_size() == 4) pri_transfer<float, false>(*this, (float *)slab.data(), (float *)image.data());
     else pri_transfer<double, false>(*this, (double *)slab.data(), (double *)image.data());
     to_dev(snap_[cur], slab.data(), snap_bytes);
 }

@@ -16,7 +16,9 @@ static void usage() {
     fprintf(stderr,
             "Usage: tclb [options] <model> <case.xml> [XPATH (=|@attr =|inject|insert|delete|print) value ...] [-s out.xml] [-x]\n"
             "Options:\n"
-            "  --precision float|double   arithmetic of the model library (default float)\n"
+            "  --precision float|double|float_half|float_halfshift|double_float|double_floatshift\n"
+            "                             arithmetic[_storage] of the model library (default float); the storage suffix is the\n"
+            "                             reference's --with-storage: half = 16-bit lattice, shift = store value minus the field's shift\n"
             "  --cpu | --gpu              backend (default gpu)\n"
             "  --ranks N                  number of subdomains (y/z decomposition, one GPU each)\n"
             "  --devices a,b,c            GPU ids for the subdomains (default: round-robin over visible GPUs)\n"

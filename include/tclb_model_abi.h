@@ -12,7 +12,7 @@
 extern "C" {
 #endif
 
-#define TCLB_ABI_VERSION 7
+#define TCLB_ABI_VERSION 8
 #define TCLB_MAX_NEIGH 9            /* (dy,dz) in {-1,0,1}^2 ; x is never decomposed */
 #define TCLB_MAX_RANKS 16           /* subdomains that exchange Globals through peer memory (one box) */
 #define TCLB_GL_RING 8              /* depth of the Globals publication ring */
@@ -113,6 +113,11 @@ typedef struct {
     int (*color)(const tclb_launch_t *);          /* out = uchar4[rny][rnx] of plane rz */
     int (*kernel_info)(int stage, int globals_mode, int *regs, int *smem, int *lmem, int *max_threads);
     const char *(*last_error)(void);
+    /* storage of the lattice in memory (reference --with-storage): element size of a snapshot value, whether the
+     * per-field shift is subtracted on store, the type name, and the shift of every field */
+    int storage_size, storage_shifted;
+    const char *storage_name;
+    const double *field_shift;
 } tclb_model_t;
 
 /* every model library exports exactly this symbol */

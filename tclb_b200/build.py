@@ -141,8 +141,27 @@ def generate_model(variant: str) -> Path:
     return out
 
 
+PRECISIONS = ("float", "double", "float_half", "float_halfshift", "double_float", "double_floatshift")
+
+
+def precision_flags(precision: str) -> List[str]:
+    """compile flags of a precision/storage combination: <real>[_<storage>] with storage in half, halfshift, float,
+    floatshift (the reference's ./configure --with-storage=half|half-shift|float|float-shift next to --enable-double;
+    plain float/double store what they compute)"""
+    if precision not in PRECISIONS:
+        raise ValueError(f"precision must be one of {PRECISIONS}")
+    real, _, storage = precision.partition("_")
+    flags = ["-DTCLB_DOUBLE"] if real == "double" else []
+    if storage.startswith("half"):
+        flags.append("-DTCLB_STORAGE_HALF")
+    if storage.startswith("float"):
+        flags.append("-DTCLB_STORAGE_FLOAT")
+    if storage.endswith("shift"):
+        flags.append("-DTCLB_STORAGE_SHIFT")
+    return flags
+
+
 def build_model_lib(variant: str, precision: str = "float", force: bool = False, verbose: bool = False) -> Path:
-    assert precision in ("float", "double")
     LIBDIR.mkdir(parents=True, exist_ok=True)
     src = generate_model(variant)
     target = LIBDIR / f"libtclb_{variant}_{precision}.so"
@@ -151,8 +170,7 @@ def build_model_lib(variant: str, precision: str = "float", force: bool = False,
     if not force and _stamp_ok(target, digest):
         return target
     cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
-    if precision == "double":
-        cmd.append("-DTCLB_DOUBLE")
+    cmd += precision_flags(precision)
     cmd += ["-o", str(target), str(src), "-lgomp"]
     log = ROOT / "build" / "logs" / f"{variant}_{precision}.ptxas.log"
     _run(cmd, log)
@@ -177,8 +195,7 @@ def build_custom(modeldef, libname: str, precision: str = "double", extra_flags=
     if _stamp_ok(target, digest):
         return target
     cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + list(extra_flags) + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
-    if precision == "double":
-        cmd.append("-DTCLB_DOUBLE")
+    cmd += precision_flags(precision)
     cmd += ["-o", str(target), str(src), "-lgomp"]
     _run(cmd, ROOT / "build" / "logs" / f"{libname}_{precision}.ptxas.log")
     _stamp(target, digest)

@@ -125,6 +125,35 @@ def emit_model_source(m: ModelDef, libname: str) -> str:
     A('#include "tclb_node_rt.h"')
     A("#ifdef TCLB_DOUBLE\ntypedef double real_t;\n#define TCLB_REAL_NAME \"double\"\n#else\ntypedef float real_t;\n#define TCLB_REAL_NAME \"float\"\n#endif")
     A("typedef tclb_vec3<real_t> vector_t;")
+    # storage type of the lattice (reference ./configure --with-storage=half|half-shift|float|float-shift|double,
+    # src/LatticeAccess.inc.cpp.Rt:14-35): what lives in HBM may be narrower than what the node code computes in, and a
+    # per-field constant (AddDensity(shift=)) may be subtracted before storing so that small deviations keep their bits
+    A(r"""#if defined(TCLB_STORAGE_HALF)
+#include <cuda_fp16.h>
+typedef __half storage_t;
+#define TCLB_STORAGE_NAME "half"
+TCLB_HD real_t storage_to_real(storage_t v) { return (real_t)__half2float(v); }
+TCLB_HD storage_t real_to_storage(real_t v) { return __float2half((float)v); }
+#elif defined(TCLB_STORAGE_FLOAT)
+typedef float storage_t;
+#define TCLB_STORAGE_NAME "float"
+#define storage_to_real(v__) ((real_t)(v__))
+#define real_to_storage(v__) ((float)(v__))
+#else
+typedef real_t storage_t;
+#define TCLB_STORAGE_NAME TCLB_REAL_NAME
+#define storage_to_real(v__) (v__)
+#define real_to_storage(v__) (v__)
+#endif
+#ifdef TCLB_STORAGE_SHIFT
+#define TCLB_LD(v__, s__) (storage_to_real(v__) + (real_t)(s__))
+#define TCLB_ST(v__, s__) real_to_storage((v__) - (real_t)(s__))
+#define TCLB_STORAGE_SHIFTED 1
+#else
+#define TCLB_LD(v__, s__) storage_to_real(v__)
+#define TCLB_ST(v__, s__) real_to_storage(v__)
+#define TCLB_STORAGE_SHIFTED 0
+#endif""")
     A(f"typedef {flag_t} flag_t;")
     A("#ifdef _OPENMP\n#include <omp.h>\n#endif")
     tun = getattr(m, "tuning", {}) or {}
@@ -162,12 +191,12 @@ struct KArgs {
     long long fstride;
     int off_x, off_y, off_z, tot_nx, tot_ny, tot_nz;
     real_t pos_x, pos_y, pos_z;
-    const real_t *in;
-    real_t *out;
+    const storage_t *in;
+    storage_t *out;
     // per-density source pointers, already shifted by the pull offset in y/z (x is handled by the wrapped
     // index), and per-field destination pointers: an access is ONE 32-bit-index IMAD.WIDE + LDG/STG
-    const real_t *ldp[N_DENSITIES];
-    real_t *stp[N_FIELDS];
+    const storage_t *ldp[N_DENSITIES];
+    storage_t *stp[N_FIELDS];
     int obj_enabled;
     const flag_t *flags;
     const uint16_t *cuts;
@@ -181,7 +210,7 @@ struct KArgs {
     const real_t *zone;
     int zone_len, zone_index, zone_stride;
     int iter, reset_iter;
-    real_t *halo[9];
+    storage_t *halo[9];
     int halo_ny[9], halo_nz[9];
     unsigned *sig_count;
     unsigned *sig_remote[9];
@@ -239,6 +268,12 @@ struct KArgs {
     for name, body in macros:
         A(f"#define {name} {body}")
     A(_lattice_tables(m.code))
+    # storage shift of every field (0 unless the model asked for one); folds to a constant after inlining
+    A("TCLB_HD real_t field_shift(int fi) {\n    switch (fi) {")
+    for i, f in enumerate(m.fields):
+        if f.shift:
+            A(f"    case {i}: return (real_t){float(f.shift)!r};")
+    A("    default: return (real_t)0;\n    }\n}")
 
     members = _member_decls([d.name for d in m.densities] + [f.name for f in m.fields])
     A(r"""
@@ -290,7 +325,7 @@ struct Node {
     TCLB_HD real_t load_field(int fi, int dx, int dy, int dz) const {
         int xx = tclbrt::wrapx(n_x, dx, ka_.nx);
         long long i = ((long long)(n_z + dz + GZ) * ka_.NY + (n_y + dy + GY)) * ka_.nx + xx;
-        return ka_.in[fi * ka_.fstride + i];
+        return TCLB_LD(ka_.in[fi * ka_.fstride + i], field_shift(fi));
     }
     TCLB_HD real_t load_field(int fi, int dx, int dy) const { return load_field(fi, dx, dy, 0); }
     TCLB_HD uint16_t getQ(int d) const {
@@ -354,7 +389,7 @@ TCLB_HD long long src_index(const KArgs &a, int x, int y, int z, int dx, int dy,
 
 // store one value into every neighbour ghost that will read it (reach known at compile time)
 template <int MINY, int MAXY, int MINZ, int MAXZ>
-TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, real_t v) {
+TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) {
 #pragma unroll
     for (int sz = -1; sz <= 1; sz++) {
 #pragma unroll
@@ -365,7 +400,7 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, real_t v) {
             if (sz > 0 && !(MINZ < 0 && z >= a.nz + MINZ)) continue;
             if (sz < 0 && !(MAXZ > 0 && z < MAXZ)) continue;
             const int d = (sy + 1) + 3 * (sz + 1);
-            real_t *dst = a.halo[d];
+            storage_t *dst = a.halo[d];
             if (!dst) continue;
             const int yy = sy > 0 ? y - a.ny : (sy < 0 ? y + a.halo_ny[d] : y);
             const int zz = sz > 0 ? z - a.nz : (sz < 0 ? z + a.halo_nz[d] : z);
@@ -375,12 +410,13 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, real_t v) {
     }
 }
 """)
+    shift_of = {f.name: float(f.shift or 0.0) for f in m.fields}
     for si, s in enumerate(m.stages):
         A(f"// stage {si}: {s.name} (main {s.main})")
         A(f"template <int GMODE> TCLB_HD void load_stage_{si}(Node<GMODE> &n, const KArgs &a, int x, int i0, int im, int ip) {{")
         for di, d in enumerate(m.densities):
             if d.load.get(s.name):
-                A(f"    n.{d.name} = a.ldp[{di}][{_xidx(d.dx)}];")
+                A(f"    n.{d.name} = TCLB_LD(a.ldp[{di}][{_xidx(d.dx)}], {shift_of[d.field]!r});")
             elif d.default is not None:
                 A(f"    n.{d.name} = (real_t){d.default!r};")
         A("}")
@@ -388,17 +424,17 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, real_t v) {
         for f in m.fields:
             if f.save.get(s.name):
                 fi = fidx[f.name]
-                A(f"    a.stp[{fi}][n.n_idx] = n.{f.name};")
+                A(f"    a.stp[{fi}][n.n_idx] = TCLB_ST(n.{f.name}, {shift_of[f.name]!r});")
         A("    if (border) {")
         for f in m.fields:
             if f.save.get(s.name) and (f.miny or f.maxy or f.minz or f.maxz):
                 fi = fidx[f.name]
-                A(f"        halo_put<{f.miny},{f.maxy},{f.minz},{f.maxz}>(a, {fi}, x, y, z, n.{f.name});")
+                A(f"        halo_put<{f.miny},{f.maxy},{f.minz},{f.maxz}>(a, {fi}, x, y, z, TCLB_ST(n.{f.name}, {shift_of[f.name]!r}));")
         A("    }")
         A("}")
     A("template <int GMODE> TCLB_HD void load_all(Node<GMODE> &n, const KArgs &a, int x, int i0, int im, int ip) {")
     for di, d in enumerate(m.densities):
-        A(f"    n.{d.name} = a.ldp[{di}][{_xidx(d.dx)}];")
+        A(f"    n.{d.name} = TCLB_LD(a.ldp[{di}][{_xidx(d.dx)}], {shift_of[d.field]!r});")
     A("}")
     A("template <int S, int GMODE> TCLB_HD void load_stage(Node<GMODE> &n, const KArgs &a, int x, int i0, int im, int ip) {")
     for si in range(len(m.stages)):
@@ -458,6 +494,7 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, real_t v) {
         A(f"    {{{_cstr(f.name)}, {_cstr(f.group)}, {_cstr(f.comment)}, {f.minx}, {f.maxx}, {f.miny}, {f.maxy}, {f.minz}, {f.maxz}, "
           f"{int(f.parameter)}, {int(f.average)}, {int(f.adjoint)}}},")
     A("};")
+    A("const double t_field_shift[] = {" + ", ".join(repr(float(f.shift or 0.0)) for f in m.fields) + "};")
     sidx = {s.name: i for i, s in enumerate(m.settings)}
     def setting_rows(tab, zonal):
         for s in tab:
@@ -514,7 +551,8 @@ const tclb_model_t t_model = {{
     {len(m.nodetypes)}, t_nodetypes, {len(m.nodetypegroups)}, t_nodegroups,
     {len(m.stages)}, t_stages, {len(m.actions)}, t_actions, {len(m.options)}, t_options,
     GY, GZ,
-    run_stage_impl, get_quantity_impl, color_impl, kernel_info_impl, last_error_impl
+    run_stage_impl, get_quantity_impl, color_impl, kernel_info_impl, last_error_impl,
+    (int)sizeof(storage_t), TCLB_STORAGE_SHIFTED, TCLB_STORAGE_NAME, t_field_shift
 }};
 }}  // namespace
 extern "C" const tclb_model_t *tclb_get_model(void) {{ return &t_model; }}

@@ -86,7 +86,9 @@ class _ModelDesc(C.Structure):
                 ("n_options", C.c_int), ("options", C.POINTER(_Option)),
                 ("gy", C.c_int), ("gz", C.c_int),
                 ("run_stage", C.c_void_p), ("get_quantity", C.c_void_p), ("color", C.c_void_p),
-                ("kernel_info", C.c_void_p), ("last_error", C.c_void_p)]
+                ("kernel_info", C.c_void_p), ("last_error", C.c_void_p),
+                ("storage_size", C.c_int), ("storage_shifted", C.c_int), ("storage_name", C.c_char_p),
+                ("field_shift", C.POINTER(C.c_double))]
 
 
 _core = None
@@ -210,11 +212,13 @@ class Model:
         self.setting_defaults.update({_s(d.zonesettings[i].name): _s(d.zonesettings[i].default_value)
                                       for i in range(d.n_zonesettings)})
         self.zone_shift, self.zone_max = int(d.zone_shift), int(d.zone_max)
+        self.storage = _s(d.storage_name)
+        self.field_shift = [float(d.field_shift[i]) if d.storage_shifted else 0.0 for i in range(d.n_fields)]
         self.gy, self.gz = int(d.gy), int(d.gz)
 
     @property
     def bytes_per_update(self) -> int:
-        return 2 * len(self.fields) * self.d.real_size + self.d.flag_size
+        return 2 * len(self.fields) * self.d.storage_size + self.d.flag_size
 
     def flag(self, *names: str) -> int:
         v = 0
