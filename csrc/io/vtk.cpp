@@ -72,7 +72,7 @@ void VtkFileOut::init(const Box &tot, const Box &r, const std::vector<std::pair<
 }
 void VtkFileOut::write_field(const std::string &name, const void *data, int elem, const char *tp, int comp) {
     if (!f_) fail("vtk writer used before opening a file");
-    int len = (int)(size_ * elem);
+    int len = (int)(size_ * elem * comp);      // elem = size of one component
     fprintf(f_, "<DataArray type=\"%s\" Name=\"%s\" format=\"binary\" encoding=\"base64\" NumberOfComponents=\"%d\">\n", tp, name.c_str(), comp);
     std::string h = base64_encode(&len, sizeof(int)), d = base64_encode(data, (size_t)len);
     fwrite(h.data(), 1, h.size(), f_);
