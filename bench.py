@@ -85,6 +85,7 @@ def main():
     ap.add_argument("--no-globals", action="store_true", help="diagnostics: skip the per-iteration Globals")
     ap.add_argument("--halo", default="direct", choices=["direct", "nccl"])
     ap.add_argument("--block", default=None, help="bx,by kernel block override")
+    ap.add_argument("--precision", default="float", help="diagnostics: arithmetic[_storage] of the library (headline: float)")
     a = ap.parse_args()
     if a.impl == "reference":
         return reference_arm()
@@ -111,7 +112,7 @@ def main():
     core().tclb_log_init(rank, 6)          # warnings and errors only: stdout carries exactly one JSON line
     shape = tuple(int(v) for v in a.shape.split(",")) if a.shape else SHAPE
     nx, ny, nz = shape
-    model = Model(a.model, "float")
+    model = Model(a.model, a.precision)
     dd = DistDomain(model, shape, rank=rank, world=world, device=local_rank, direct=(a.halo == "direct"))
     d = dd.domain
     if a.block:
@@ -191,12 +192,13 @@ def main():
         out = {
             "metric": "MLUPS (whole box, device-timed, max over ranks)", "value": round(value, 1), "unit": "MLUPS",
             "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms_max / a.steps, 4),
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "fp32" if a.precision == "float" else a.precision, "data": "synthetic",
             "impl": "ours",
             "config": {"model": a.model, "case": "turbulent channel (y walls, body force), Globals every iteration" if use_globals else "no globals",
                        "lattice": list(shape), "global_batch": int(nodes), "seq_len": None,
                        "parallelism": f"domain-decomposition y{d.divy}xz{d.divz}", "halo": "fused P2P stores" if a.halo == "direct" else "nccl baseline",
-                       "l2": "working set 2x%.1f GB per job >> 126 MB L2, no flush needed" % (nodes * len(model.fields) * 4 / 1e9)},
+                       "l2": "working set 2x%.1f GB per job >> 126 MB L2, no flush needed" % (nodes * len(model.fields) * model.d.storage_size / 1e9)},
             "clocks": sampler.result(),
             "e2e": {"value": round(e2e_value, 1), "unit": "MLUPS", "steps": e2e_steps, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes},
             "gpu_launches": a.steps * len(model.actions["Iteration"]),
