@@ -92,11 +92,12 @@ Lattice::~Lattice() {
         if (stream && owns_stream_) cudaStreamDestroy((cudaStream_t)stream);
         if (zone_dev_) cudaFree(zone_dev_);
         if (cuts_dev_) cudaFree(cuts_dev_);
+        if (particles_dev_) cudaFree(particles_dev_);
         if (st_dev_) cudaFree(st_dev_);
         if (scratch_) cudaFree(scratch_);
         if (pinned_) cudaFreeHost(pinned_);
     } else {
-        free(zone_dev_); free(cuts_dev_); free(st_dev_); free(scratch_);
+        free(zone_dev_); free(cuts_dev_); free(st_dev_); free(scratch_); free(particles_dev_);
     }
 }
 
@@ -132,6 +133,36 @@ void *Lattice::scratch(size_t bytes) {
     }
     scratch_bytes_ = bytes;
     return scratch_;
+}
+// ---- particles ---------------------------------------------------------------------------
+void Lattice::set_particles(const std::vector<double> &rows) {
+    const int n = (int)(rows.size() / 16), rs = model->real_size();
+    if (n > particles_cap_) {
+        if (backend == TCLB_BACKEND_CUDA) {
+            TCLB_CUDA(cudaSetDevice(device));
+            sync();
+            if (particles_dev_) TCLB_CUDA(cudaFree(particles_dev_));
+            TCLB_CUDA(cudaMalloc(&particles_dev_, (size_t)n * 2 * 16 * rs));
+        } else {
+            free(particles_dev_);
+            particles_dev_ = malloc((size_t)n * 2 * 16 * rs);
+        }
+        particles_cap_ = n * 2;
+    }
+    n_particles_ = n;
+    if (n == 0) return;
+    if (rs == 4) { std::vector<float> f(rows.begin(), rows.end()); to_dev(particles_dev_, f.data(), f.size() * 4); }
+    else to_dev(particles_dev_, rows.data(), rows.size() * 8);
+}
+void Lattice::get_particles(std::vector<double> &rows) {
+    const int rs = model->real_size();
+    rows.assign((size_t)n_particles_ * 16, 0.0);
+    if (n_particles_ == 0) return;
+    if (rs == 4) {
+        std::vector<float> f(rows.size());
+        to_host(f.data(), particles_dev_, f.size() * 4);
+        for (size_t i = 0; i < f.size(); i++) rows[i] = f[i];
+    } else to_host(rows.data(), particles_dev_, rows.size() * 8);
 }
 void *Lattice::field_ptr(int snap, int field) const {
     return (char *)snap_[snap] + (size_t)field * plane_elems * model->storage_size();
@@ -374,6 +405,7 @@ void Lattice::fill_launch(tclb_launch_t &L) const {
     L.iter = iter; L.reset_iter = reset_iter;
     L.st_modes = (const tclb_st_mode_t *)st_dev_; L.st_n = st_n_;
     L.block_x = block_x; L.block_y = block_y;
+    L.particles = particles_dev_; L.n_particles = n_particles_;
     L.scale = 1.0;
     L.obj_enabled = obj_enabled_ ? 1 : 0;
 }
@@ -687,9 +719,14 @@ void Domain::copy_exchange(int s) {
 void Domain::run_action(int action, int gmode) {
     const tclb_action_t &a = model->d->actions[action];
     int tab0 = lat[local[0]]->cur, tab1 = tab0 ^ 1;
+    int first_particle = -1, last_particle = -1;
+    for (int s = 0; s < a.n_stages; s++)
+        if (model->d->stages[a.stages[s]].particle) { if (first_particle < 0) first_particle = s; last_particle = s; }
     for (int s = 0; s < a.n_stages; s++) {
         int in = s == 0 ? tab0 : tab1;
+        if (s == first_particle && particles_in_hook) particles_in_hook();
         for (int r : local) lat[r]->launch_stage(a.stages[s], in, tab1, gmode, s == a.n_stages - 1);
+        if (s == last_particle && particles_out_hook) particles_out_hook();
         bool need_copy = false;
         for (int r : local) if (lat[r]->halo_mode == TCLB_HALO_NONE) need_copy = true;
         if (need_copy) {

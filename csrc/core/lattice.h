@@ -99,6 +99,11 @@ class Lattice {
     void set_setting(int idx, double v);                   // applies derived-settings chain
     double get_setting(int idx) const { return settings[idx]; }
     void set_synthetic_turbulence(const std::vector<tclb_st_mode_t> &modes);
+    // ---- particles (reference Lattice::CopyInParticles/CopyOutParticles, src/Lattice.cu.Rt:392-437) ----
+    // rows of 16 doubles in the RFI layout (r, pos, vel, angular velocity, force, moment); forces start at zero
+    void set_particles(const std::vector<double> &rows16);
+    void get_particles(std::vector<double> &rows16);        // after the particle stages: force/moment filled in
+    int n_particles() const { return n_particles_; }
     // ---- execution ----
     void launch_stage(int stage, int in_snap, int out_snap, int globals_mode, bool publish_globals = true);
     void clear_globals();
@@ -131,6 +136,8 @@ class Lattice {
     void *cuts_dev_;
     void *st_dev_;
     int st_n_;
+    void *particles_dev_ = nullptr;   // real_t[n_particles_][16]
+    int n_particles_ = 0, particles_cap_ = 0;
     bool owns_stream_ = false;
     void *pinned_ = nullptr;       // page-locked staging: [0,half) host->device, [half,end) device->host
     size_t pinned_bytes_ = 0;
@@ -168,6 +175,9 @@ class Domain {
     // hooks for multi-process operation
     std::function<void(int /*epoch*/)> exchange_hook;       // HALO_NONE: external (NCCL/gloo) exchange after every stage
     std::function<void(double *, int, int)> reduce_hook;    // (values, count, op) across processes
+    // particle coupling: called around the particle stages of an action (before the first: load the particles of every
+    // local subdomain; after the last: hand the forces back)
+    std::function<void()> particles_in_hook, particles_out_hook;
 
     void connect_local();                  // publish local lattices to each other (enables peer access)
     void set_peer(int local_rank, int peer_rank, const PeerInfo &p);

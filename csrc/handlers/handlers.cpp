@@ -860,6 +860,53 @@ TCLB_REGISTER_HANDLER("SaveBinary", CbSaveBinary)
 class CbSaveMemoryDump : public CbSaveBinary {};
 TCLB_REGISTER_HANDLER("SaveMemoryDump", CbSaveMemoryDump)
 
+// <RemoteForceInterface integrator="SIMPLEPART" [omega torque]>: particle coupling.  The reference connects to an external
+// program over MPI inter-communicators (acRemoteForceInterface.cpp:7-110); here the integrator runs in this process
+// (csrc/host/particles.h).  Its configuration is the <SimplePart> child element, or the file given with --simplepart.
+class AcRemoteForceInterface : public Action {
+  public:
+    int init() override {
+        Action::init();
+        std::string name = node->attr("integrator");
+        if (name.empty()) { logf(L_ERROR, "You must specify RemoteForceInterface integrator name"); return -1; }
+        if (name != "SIMPLEPART" && name != "simplepart") {
+            logf(L_ERROR, "RemoteForceInterface: integrator %s is not available (built in: SIMPLEPART)", name.c_str());
+            return -1;
+        }
+        std::unique_ptr<XmlDocument> doc;
+        const XmlNode *cfg = node->child("SimplePart");
+        if (!solver->opt.simplepart_config.empty()) {
+            doc.reset(new XmlDocument());
+            doc->load_file(solver->opt.simplepart_config);
+            cfg = doc->child("SimplePart");
+        }
+        if (!cfg) { logf(L_ERROR, "RemoteForceInterface: no <SimplePart> configuration (child element or --simplepart file)"); return -1; }
+        logf(L_OUTPUT, "Connecting RFI to %s (in-process)", name.c_str());
+        solver->integrator.reset(new SimplePart(cfg, solver->outpath + "_SP_Log.csv", node->attr_bool("omega"), node->attr_bool("torque")));
+        Solver *s = solver;
+        auto box_of = [s](int r) {
+            const Box &b = s->domain->dec.boxes[r];
+            WorkerBox w;
+            w.lower[0] = s->px + b.x0; w.upper[0] = s->px + b.x0 + b.nx;
+            w.lower[1] = s->py + b.y0; w.upper[1] = s->py + b.y0 + b.ny;
+            w.lower[2] = s->pz + b.z0; w.upper[2] = s->pz + b.z0 + b.nz;
+            return w;
+        };
+        solver->domain->particles_in_hook = [s, box_of]() {
+            s->integrator->begin_exchange();
+            std::vector<double> rows;
+            for (int r : s->domain->local) { s->integrator->particles_for(box_of(r), rows); s->domain->lat[r]->set_particles(rows); }
+        };
+        solver->domain->particles_out_hook = [s, box_of]() {
+            std::vector<double> rows;
+            for (int r : s->domain->local) { s->domain->lat[r]->get_particles(rows); s->integrator->forces_from(box_of(r), rows); }
+            s->integrator->step();
+        };
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("RemoteForceInterface", AcRemoteForceInterface)
+
 // <RunPython> / <RunR> (reference src/Handlers/cbRunR.cpp): the code runs inside the embedding Python process through
 // the script hook (tclb_solver_set_script_hook; tclb_b200.runtime.Solver installs one that exposes the same object
 // surface: Solver.Settings/Fields/Quantities/Globals/Geometry/Actions/Info).  Without a hook (plain bin/tclb) the

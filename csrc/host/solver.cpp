@@ -574,6 +574,7 @@ int Solver::run() {
     if (!h) { logf(L_ERROR, "Something went wrong in xml run!"); return -1; }
     h.reset();
     domain->sync();
+    if (integrator) { integrator->finish(); integrator.reset(); domain->particles_in_hook = nullptr; domain->particles_out_hook = nullptr; }
     if (is_root()) {
         double d = walltime();
         logf(L_OUTPUT, "Total duration: %lf s = %lf min = %lf h", d, d / 60, d / 3600);

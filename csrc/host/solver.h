@@ -13,6 +13,7 @@
 #include "../core/lattice.h"
 #include "../core/model.h"
 #include "geometry.h"
+#include "particles.h"
 #include "units.h"
 #include "xml.h"
 
@@ -44,6 +45,7 @@ struct SolverOptions {
     bool direct_halo = true;
     std::string model_path;            // explicit library path (optional)
     int x_block = -1;                  // nx padding granule (-1: 32 on CUDA, 1 on CPU)
+    std::string simplepart_config;     // <SimplePart> XML file for <RemoteForceInterface integrator="SIMPLEPART"> (bin/tclb --simplepart)
 };
 
 class Solver {
@@ -67,6 +69,7 @@ class Solver {
     std::vector<double> log_scales;
     double px = 0, py = 0, pz = 0;
     bool stop_requested = false;
+    std::unique_ptr<ParticleIntegrator> integrator;    // particle coupling (<RemoteForceInterface>)
     // in-process scripting hook (<RunPython>/<RunR>): set by the embedding program, called with the element name, the
     // code (text of the element or of its file= attribute) and the iteration; a non-zero return aborts the run
     int (*script_hook)(void *user, const char *element, const char *code, int iteration) = nullptr;

@@ -229,19 +229,21 @@ def build_from_dir(model_dir: str, name: Optional[str] = None, precision: str = 
 # models of a mounted TCLB tree that are built next to the native ones when the tree is present
 REFERENCE_ROOT = Path(os.environ.get("TCLB_REFERENCE", "/root/reference"))
 REFERENCE_MODELS = ["multiphase/d3q27_pf_velocity", "flow/d2q9", "flow/d3q19", "flow/d3q27_cumulant", "heat/d3q19_heat",
-                    "electrokinetic/d2q9_poison_boltzmann", "electrokinetic/d2q9_npe_guo", "multiphase/d2q9_kuper"]
+                    "electrokinetic/d2q9_poison_boltzmann", "electrokinetic/d2q9_npe_guo", "multiphase/d2q9_kuper",
+                    "particles/d3q27_PSM:NEBB"]            # "<directory>[:<option>,...]"
 
 
 def build_reference_models(precisions=("float", "double"), verbose=False) -> List[Path]:
     out = []
     if not (REFERENCE_ROOT / "models").is_dir():
         return out
-    for rel in REFERENCE_MODELS:
+    for entry in REFERENCE_MODELS:
+        rel, _, optlist = entry.partition(":")
         d = REFERENCE_ROOT / "models" / rel
         if not d.is_dir():
             continue
         for p in precisions:
-            out.append(build_from_dir(str(d), precision=p))
+            out.append(build_from_dir(str(d), precision=p, options={o: True for o in optlist.split(",") if o}))
             if verbose:
                 print(f"built {out[-1]}")
     return out

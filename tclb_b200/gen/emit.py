@@ -107,6 +107,91 @@ def _lattice_tables(code: str) -> str:
     return "\n".join(out)
 
 
+# Particle access for model code (reference src/Particle.hpp:1-150 + the SolidAll container, src/SolidAll.h): a range
+# over the particles whose padded bounding box contains the node; `for (auto p : SyncParticleIterator(X,Y,Z))` gets one
+# object per particle with p.diff, p.cvel, p.rad, p.dist, p.applyForce(f); force and moment are added to the particle
+# row when the object goes out of scope.  The container is the brute-force one (every particle is tested), which is what
+# the reference configures by default; accumulation is one atomic per component and contributing node.
+_PARTICLES = r"""
+#define RFI_DATA_R 0
+#define RFI_DATA_POS 1
+#define RFI_DATA_VEL 4
+#define RFI_DATA_ANGVEL 7
+#define RFI_DATA_FORCE 10
+#define RFI_DATA_MOMENT 13
+#define RFI_DATA_SIZE 16
+#define PART_MAR ((real_t)@PART_MAR@)
+TCLB_HD void particle_atomic_add(real_t *p, real_t v) {
+#ifdef __CUDA_ARCH__
+    atomicAdd(p, v);
+#else
+#pragma omp atomic
+    *p += v;
+#endif
+}
+struct Particle {
+    vector_t cvel, diff;
+    real_t rad, dist;
+    TCLB_HD bool in() const { return dist < rad; }
+};
+struct ParticleI : Particle {
+    real_t *row;
+    TCLB_HD ParticleI(real_t *row_, real_t x, real_t y, real_t z) : row(row_) {
+        rad = row[RFI_DATA_R];
+        diff.x = x - row[RFI_DATA_POS + 0]; diff.y = y - row[RFI_DATA_POS + 1]; diff.z = z - row[RFI_DATA_POS + 2];
+        dist = sqrt(diff.x * diff.x + diff.y * diff.y + diff.z * diff.z);
+        const real_t ox = row[RFI_DATA_ANGVEL + 0], oy = row[RFI_DATA_ANGVEL + 1], oz = row[RFI_DATA_ANGVEL + 2];
+        cvel.x = row[RFI_DATA_VEL + 0] + oy * diff.z - oz * diff.y;
+        cvel.y = row[RFI_DATA_VEL + 1] + oz * diff.x - ox * diff.z;
+        cvel.z = row[RFI_DATA_VEL + 2] + ox * diff.y - oy * diff.x;
+    }
+};
+struct ParticleS : ParticleI {
+    vector_t force, moment;
+    bool touched;
+    TCLB_HD ParticleS(real_t *row_, real_t x, real_t y, real_t z) : ParticleI(row_, x, y, z), touched(false) {
+        force.x = force.y = force.z = 0;
+        moment.x = moment.y = moment.z = 0;
+    }
+    TCLB_HD void applyForce(vector_t f) {
+        force.x += f.x; force.y += f.y; force.z += f.z;
+        moment.x -= f.y * diff.z - f.z * diff.y;
+        moment.y -= f.z * diff.x - f.x * diff.z;
+        moment.z -= f.x * diff.y - f.y * diff.x;
+        touched = true;
+    }
+    TCLB_HD ~ParticleS() {
+        if (!touched) return;
+        particle_atomic_add(row + RFI_DATA_FORCE + 0, force.x); particle_atomic_add(row + RFI_DATA_FORCE + 1, force.y);
+        particle_atomic_add(row + RFI_DATA_FORCE + 2, force.z);
+        particle_atomic_add(row + RFI_DATA_MOMENT + 0, moment.x); particle_atomic_add(row + RFI_DATA_MOMENT + 1, moment.y);
+        particle_atomic_add(row + RFI_DATA_MOMENT + 2, moment.z);
+    }
+};
+template <class P>
+struct ParticleRange {
+    real_t *data;
+    int n;
+    real_t x, y, z;
+    TCLB_HD bool near(int i) const {
+        const real_t *row = data + (size_t)i * RFI_DATA_SIZE;
+        const real_t rr = row[RFI_DATA_R] + PART_MAR;
+        return fabs(x - row[RFI_DATA_POS + 0]) <= rr && fabs(y - row[RFI_DATA_POS + 1]) <= rr && fabs(z - row[RFI_DATA_POS + 2]) <= rr;
+    }
+    struct It {
+        const ParticleRange *r;
+        int i;
+        TCLB_HD void skip() { while (i < r->n && !r->near(i)) i++; }
+        TCLB_HD P operator*() const { return P(r->data + (size_t)i * RFI_DATA_SIZE, r->x, r->y, r->z); }
+        TCLB_HD It &operator++() { i++; skip(); return *this; }
+        TCLB_HD bool operator!=(const It &o) const { return i != o.i; }
+    };
+    TCLB_HD It begin() const { It it{this, 0}; it.skip(); return it; }
+    TCLB_HD It end() const { return It{this, n}; }
+};
+"""
+
+
 def emit_model_source(m: ModelDef, libname: str) -> str:
     """Return the text of the generated .cu file (precision chosen by -DTCLB_DOUBLE)."""
     m.finalize()
@@ -223,6 +308,8 @@ struct KArgs {
     real_t qscale;
     const tclb_st_mode_t *st;
     int st_n;
+    real_t *particles;           // [n_particles][16]: r, pos, vel, angular velocity, force, moment (RFI layout)
+    int n_particles;
     real_t settings[N_SETTINGS > 0 ? N_SETTINGS : 1];
 };
 """)
@@ -268,6 +355,7 @@ struct KArgs {
     for name, body in macros:
         A(f"#define {name} {body}")
     A(_lattice_tables(m.code))
+    A(_PARTICLES.replace("@PART_MAR@", repr(float(getattr(m, "part_margin", None) or 0.5))))
     # storage shift of every field (0 unless the model asked for one); folds to a constant after inlining
     A("TCLB_HD real_t field_shift(int fi) {\n    switch (fi) {")
     for i, f in enumerate(m.fields):
@@ -328,6 +416,12 @@ struct Node {
         return TCLB_LD(ka_.in[fi * ka_.fstride + i], field_shift(fi));
     }
     TCLB_HD real_t load_field(int fi, int dx, int dy) const { return load_field(fi, dx, dy, 0); }
+    TCLB_HD ParticleRange<ParticleS> SyncParticleIterator(real_t x, real_t y, real_t z) const {
+        return ParticleRange<ParticleS>{ka_.particles, ka_.n_particles, x, y, z};
+    }
+    TCLB_HD ParticleRange<ParticleI> ParticleIterator(real_t x, real_t y, real_t z) const {
+        return ParticleRange<ParticleI>{ka_.particles, ka_.n_particles, x, y, z};
+    }
     TCLB_HD uint16_t getQ(int d) const {
         return ka_.cuts ? ka_.cuts[(long long)d * ((long long)ka_.nx * ka_.NY * ka_.NZ) + n_idx] : (uint16_t)NO_CUT;
     }

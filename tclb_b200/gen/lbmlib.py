@@ -104,6 +104,7 @@ def mrt_eq(U, rho="rho", J=("Jx", "Jy", "Jz"), sigma2=1.0 / 3.0, order: int = 2,
     Jnames = []
     for j in Jv:
         Jnames.extend(j.symbols())
+    rho_syms = set(rho_p.symbols())
     B = poly_moment_matrix(U)
     H = []
     from fractions import Fraction
@@ -115,7 +116,10 @@ def mrt_eq(U, rho="rho", J=("Jx", "Jy", "Jz"), sigma2=1.0 / 3.0, order: int = 2,
                 h = h * Jv[i] * rho_p ** -1
             elif B.p[j, i] == 2:
                 h = h * (Jv[i] ** 2 * rho_p ** -2 + s2)
-        H.append(h.truncate(Jnames, order))
+        # order of a term = total |power| of every symbol except the density's (reference src/lib/feq.R:50-57): the
+        # momentum may be given as a product such as d*u[0], whose density factor must not count
+        count = [sy for sy in h.symbols() if sy not in rho_syms]
+        H.append(h.truncate(count, order))
     Req = PVec(H)
     Mat = B.mat
     ordr = B.order.copy()

@@ -622,7 +622,9 @@ def install_poly(I):
         out = []
         for i in range(n):
             toks = [p[i % len(p)] for p in parts]
-            if len(toks) == 1 and not isinstance(toks[0], str):
+            if len(toks) == 1 and toks[0] is None:
+                out.append(Poly.sym("NA"))
+            elif len(toks) == 1 and not isinstance(toks[0], str):
                 out.append(Poly.const(float(toks[0])))
             else:
                 out.append(Poly.sym("".join(to_str(t) for t in toks)))

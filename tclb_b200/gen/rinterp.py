@@ -587,6 +587,13 @@ class Interp:
             return sub
         names = self.names_of(x)
         pos = self._pos_index(idxs[0], a.size, names)
+        if len(pos) and max(pos) >= a.size:
+            # R: indexing past the end of a vector gives NA, not an error
+            ext = np.empty(max(pos) + 1, dtype=object)
+            ext[:a.size] = a.tolist()
+            ext[a.size:] = None
+            a = ext
+            names = None
         out = a[pos] if len(pos) else a[:0]
         if names:
             out = NamedVec(out, [names[i] for i in pos])

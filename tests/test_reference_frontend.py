@@ -81,3 +81,15 @@ def test_reference_test_suite_files_pass_with_the_runner(reference_dir, tclb_bin
     r = subprocess.run(["python", os.path.join(root, "tools", "run_tests.py"), "d2q9", os.path.join(reference_dir, "tests/external/d2q9")],
                        capture_output=True, text=True, timeout=1800)
     assert r.returncode == 0 and "5 of 5 tests passed" in r.stdout, r.stdout[-3000:]
+
+
+def test_reference_particle_suite_passes(reference_dir, tclb_bin):
+    """tests/external/d3q27_PSM_NEBB: partially-saturated-cell particles (model lowered from the reference's files, NEBB
+    option) coupled to the built-in SimplePart integrator: fluid log, particle force log and the VTK fields (with a
+    periodic shift for the particle placed on the corner) against the goldens"""
+    from tclb_b200 import build
+    build.build_from_dir(os.path.join(reference_dir, "models/particles/d3q27_PSM"), precision="double", options={"NEBB": True})
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run(["python", os.path.join(root, "tools", "run_tests.py"), "d3q27_PSM_NEBB", os.path.join(reference_dir, "tests/external/d3q27_PSM_NEBB"),
+                        "--library", "ref_d3q27_PSM_NEBB"], capture_output=True, text=True, timeout=1800)
+    assert r.returncode == 0 and "3 of 3 tests passed" in r.stdout, r.stdout[-3000:]
