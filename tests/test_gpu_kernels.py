@@ -185,3 +185,48 @@ def test_gpu_reference_pf_velocity_matches_cpu_oracle(tclb_bin, tmp_path):
             assert abs(x - y) <= 1e-9 * max(abs(x), abs(y)) + 1e-11, (n, x, y)
     liq = [float(r[hdr.index("LiqTotalPhase")]) for r in logs["gpu"][1:]]
     assert liq[0] > 100 and abs(liq[-1] - liq[0]) < 0.05 * liq[0]
+
+
+def test_gpu_particles_match_cpu_oracle(tclb_bin, tmp_path):
+    """particle stages on the GPU (atomic force accumulation, periodic images of a particle on the corner) against the
+    CPU oracle: fluid log and particle force log of the PSM model lowered from the reference's files"""
+    import csv
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.exists(os.path.join(root, "tclb_b200", "_lib", "libtclb_ref_d3q27_PSM_NEBB_double.so")):
+        pytest.skip("ref_d3q27_PSM_NEBB was not built (no reference tree at build time)")
+    case = """<?xml version="1.0"?>
+<CLBConfig version="2.0" permissive="true" output="output/">
+  <Geometry nx="32" ny="24" nz="16"><BGK><Box/></BGK></Geometry>
+  <Model>
+    <Param name="nu" value="0.03"/>
+    <RemoteForceInterface integrator="SIMPLEPART">
+      <SimplePart dt="1" ax="0.001" afreq="0.01">
+        <Particle x="1" y="12" z="0" r="4" log="y"/>
+        <Particle x="20" y="6" z="9" r="3" vy="0.002" log="y"/>
+        <Periodic x="32" y="24" z="16"/>
+        <Log name="output/forces.csv" Iterations="1"/>
+      </SimplePart>
+    </RemoteForceInterface>
+  </Model>
+  <Log Iterations="5"/>
+  <Solve Iterations="30"/>
+</CLBConfig>
+"""
+    out = {}
+    for backend in ("cpu", "gpu"):
+        wd = tmp_path / backend
+        wd.mkdir()
+        (wd / "p.xml").write_text(case)
+        r = subprocess.run([tclb_bin, f"--{backend}", "--precision", "double", "ref_d3q27_PSM_NEBB", "p.xml"], cwd=wd, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        out[backend] = [list(csv.reader(open(wd / "output" / f))) for f in ("forces.csv", "p_Log_P00_00000000.csv")]
+    for a, b in zip(out["cpu"], out["gpu"]):
+        assert a[0] == b[0] and len(a) == len(b) > 5
+        for ra, rb in zip(a[1:], b[1:]):
+            for n, x, y in zip(a[0], ra, rb):
+                if n == "Walltime":
+                    continue
+                assert abs(float(x) - float(y)) <= 1e-9 * max(abs(float(x)), abs(float(y))) + 1e-12, (n, x, y)
+    fx = [abs(float(r[8])) for r in out["gpu"][0][1:]]
+    assert max(fx) > 1e-3                                   # the particles do exchange momentum with the fluid
