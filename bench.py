@@ -85,6 +85,7 @@ def main():
     ap.add_argument("--no-globals", action="store_true", help="diagnostics: skip the per-iteration Globals")
     ap.add_argument("--halo", default="direct", choices=["direct", "nccl"])
     ap.add_argument("--block", default=None, help="bx,by kernel block override")
+    ap.add_argument("--no-graph", action="store_true", help="diagnostics: plain launches instead of the replayed CUDA graph")
     ap.add_argument("--precision", default="float", help="diagnostics: arithmetic[_storage] of the library (headline: float)")
     a = ap.parse_args()
     if a.impl == "reference":
@@ -115,6 +116,8 @@ def main():
     model = Model(a.model, a.precision)
     dd = DistDomain(model, shape, rank=rank, world=world, device=local_rank, direct=(a.halo == "direct"))
     d = dd.domain
+    if a.no_graph:
+        d.use_graphs(False)
     if a.block:
         bx, by = (int(v) for v in a.block.split(","))
         d.set_block(bx, by)
@@ -201,7 +204,8 @@ def main():
                        "l2": "working set 2x%.1f GB per job >> 126 MB L2, no flush needed" % (nodes * len(model.fields) * model.d.storage_size / 1e9)},
             "clocks": sampler.result(),
             "e2e": {"value": round(e2e_value, 1), "unit": "MLUPS", "steps": e2e_steps, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes},
-            "gpu_launches": a.steps * len(model.actions["Iteration"]),
+            "gpu_launches": a.steps * len(model.actions["Iteration"]) * (3 if use_globals else 1),
+            "graph_iterations": d.graph_iterations,
             "roofline": {"bytes_per_update": bytes_per_update, "achieved_gbs_per_gpu": round(value * 1e6 * bytes_per_update / 1e9 / a.gpus, 1),
                          "hbm_gbs_measured": hbm, "fraction_of_measured_hbm": round(value * 1e6 * bytes_per_update / 1e9 / a.gpus / hbm, 3)},
             "globals_sample": {k: g[k] for k in list(g)[:4]}, "last_e2e_flux": last,

@@ -165,6 +165,10 @@ int tclb_domain_reset_average(tclb_domain_h *h) {
     for (int r : h->d->local) h->d->lat[r]->reset_iter = h->d->lat[r]->iter;
     GUARD_END_INT
 }
+int tclb_domain_use_graphs(tclb_domain_h *h, int on) {
+    GUARD_BEGIN h->d->use_graphs = on != 0; if (!on) h->d->drop_graphs(); GUARD_END_INT
+}
+long long tclb_domain_graph_iterations(tclb_domain_h *h) { return h->d->graph_replays; }
 int tclb_domain_set_block(tclb_domain_h *h, int bx, int by) {
     GUARD_BEGIN
     for (int r : h->d->local) { h->d->lat[r]->block_x = bx; h->d->lat[r]->block_y = by; }

@@ -47,7 +47,9 @@ Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &loca
             gl_partial_stride_ = std::max(gl_partial_stride_, 4LL * ((nx + bx - 1) / bx) * ((ny + by - 1) / by) * nz);
         }
     int sp = arena_.reserve((size_t)gl_partial_stride_ * std::max(1, m->d->n_globals) * m->real_size(), "globals partials");
+    int sd = arena_.reserve(64, "graph iteration/epoch");
     arena_.finalize();
+    dyn_dev_ = (int *)arena_.ptr(sd);
     gl_partial_ = gl_partial_stride_ > 0 ? arena_.ptr(sp) : nullptr;
     gl_ring_ = (double *)arena_.ptr(sr);
     snap_[0] = arena_.ptr(s0); snap_[1] = arena_.ptr(s1);
@@ -197,6 +199,7 @@ void Lattice::get_flags(const Box &b, uint32_t *out) const {
 void Lattice::cuts_overwrite(const uint16_t *cuts) {
     size_t bytes = (size_t)26 * plane_elems * sizeof(uint16_t);
     if (!cuts) return;
+    graph_version++;
     if (!cuts_dev_) {
         if (backend == TCLB_BACKEND_CUDA) { TCLB_CUDA(cudaSetDevice(device)); TCLB_CUDA(cudaMalloc(&cuts_dev_, bytes)); }
         else cuts_dev_ = malloc(bytes);
@@ -323,6 +326,7 @@ void Lattice::set_setting(int idx, double v) {
     // value, then every setting derived from it, transitively (reference Lattice::SetSetting
     // src/Lattice.cu.Rt:1350-1358 chains the generated DF_<name> functions the same way)
     int guard = 0;
+    graph_version++;                       // settings travel by value in the captured kernel parameters
     while (idx >= 0 && guard++ < 64) {
         settings[idx] = v;
         const tclb_setting_t &s = model->d->settings[idx];
@@ -344,6 +348,7 @@ void Lattice::set_synthetic_turbulence(const std::vector<tclb_st_mode_t> &modes)
     }
     if (bytes) to_dev(st_dev_, modes.data(), bytes);
     st_n_ = (int)modes.size();
+    graph_version++;
 }
 void Lattice::upload_zone_table_if_dirty() {
     if (!zs.dirty() && zone_dev_) return;
@@ -382,6 +387,7 @@ void Lattice::upload_zone_table_if_dirty() {
     to_dev(zone_dev_, src, bytes);
     last_h2d_bytes = bytes;
     zone_stride_ = stride;
+    graph_version++;
     zs.clear_dirty();
 }
 
@@ -421,6 +427,7 @@ void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode, bool
     L.sig_epoch = epoch;
     L.sig_enable = (sig_enable && halo_mode == TCLB_HALO_DIRECT) ? 1 : 0;
     L.sig_count = sig_ + 9;
+    if (capturing) { L.dyn = dyn_dev_; L.dyn_iter_off = cap_iter_off; L.dyn_epoch_off = epoch - cap_epoch_base; }
     L.gl_counter = gl_counter_;
     L.gl_partial = gl_partial_; L.gl_partial_stride = gl_partial_stride_;
     L.gl_epoch = epoch;
@@ -610,6 +617,7 @@ Domain::Domain(Model *m, int backend_, int nx, int ny, int nz, int nranks, const
 }
 Domain::~Domain() {
     try { sync(); } catch (...) {}
+    drop_graphs();
     for (size_t i = lat.size(); i-- > 0;) delete lat[i];     // stream owners (first on a device) go last
 }
 static int opposite(int d) {
@@ -743,8 +751,92 @@ void Domain::init() {
     iter = 0;
     run_action(a, TCLB_GLOBALS_NONE);
 }
+// ---- the iteration loop as a CUDA graph ------------------------------------------------------
+extern "C" int tclb_dyn_set(int *dyn, int iter, unsigned epoch, void *stream);
+extern "C" int tclb_dyn_advance(int *dyn, int diter, unsigned depoch, void *stream);
+
+unsigned long Domain::graph_key() const {
+    unsigned long k = 1469598103934665603ul;
+    for (int r : local) {
+        const Lattice *l = lat[r];
+        for (unsigned long v : {l->graph_version, (unsigned long)l->reset_iter, (unsigned long)l->block_x, (unsigned long)l->block_y,
+                                (unsigned long)l->halo_mode, (unsigned long)l->sig_enable, (unsigned long)(size_t)l->stream})
+            k = (k ^ v) * 1099511628211ul;
+    }
+    return k;
+}
+bool Domain::graph_possible(int action) const {
+    if (!use_graphs || backend != TCLB_BACKEND_CUDA || local.empty() || getenv("TCLB_NO_GRAPH")) return false;
+    const tclb_action_t &a = model->d->actions[action];
+    for (int s = 0; s < a.n_stages; s++) if (model->d->stages[a.stages[s]].particle) return false;
+    for (int r : local) {
+        const Lattice *l = lat[r];
+        if (l->halo_mode != TCLB_HALO_DIRECT) return false;                    // the copy/NCCL exchange runs on the host
+        if (l->device != lat[local[0]]->device || l->stream != lat[local[0]]->stream) return false;   // one stream to capture
+    }
+    return true;
+}
+void Domain::drop_graphs() {
+    for (auto &g : graph_) {
+        if (g.exec) cudaGraphExecDestroy((cudaGraphExec_t)g.exec);
+        g = GraphSlot();
+    }
+}
+void Domain::run_graph_pairs(int action, int pairs) {
+    Lattice *l0 = lat[local[0]];
+    cudaStream_t st = (cudaStream_t)l0->stream;
+    TCLB_CUDA(cudaSetDevice(l0->device));
+    for (int r : local) lat[r]->upload_zone_table_if_dirty();
+    const int o = l0->cur & 1;
+    const unsigned long key = graph_key();
+    GraphSlot &g = graph_[o];
+    if (!g.exec || g.key != key || g.action != action) {
+        if (g.exec) { cudaGraphExecDestroy((cudaGraphExec_t)g.exec); g.exec = nullptr; }
+        // capture two iterations (snapshot 0->1 and 1->0); iteration and epoch are read from device memory + offsets
+        const int iter0 = iter;
+        std::vector<unsigned> epoch0;
+        for (int r : local) { epoch0.push_back(lat[r]->epoch); lat[r]->capturing = true; lat[r]->cap_epoch_base = lat[r]->epoch; }
+        cudaGraph_t graph = nullptr;
+        TCLB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        try {
+            for (int k = 0; k < 2; k++) {
+                for (int r : local) lat[r]->cap_iter_off = k;
+                run_action(action, TCLB_GLOBALS_NONE);
+            }
+            g.launches = lat[local[0]]->epoch - epoch0[0];
+            for (int r : local)
+                if (tclb_dyn_advance(lat[r]->dyn_dev(), 2, lat[r]->epoch - lat[r]->cap_epoch_base, st) != 0) fail("graph capture: advance kernel failed");
+        } catch (...) {
+            cudaStreamEndCapture(st, &graph);
+            if (graph) cudaGraphDestroy(graph);
+            for (size_t i = 0; i < local.size(); i++) { lat[local[i]]->capturing = false; lat[local[i]]->epoch = epoch0[i]; }
+            throw;
+        }
+        TCLB_CUDA(cudaStreamEndCapture(st, &graph));
+        cudaGraphExec_t exec = nullptr;
+        TCLB_CUDA(cudaGraphInstantiate(&exec, graph, 0));
+        cudaGraphDestroy(graph);
+        // nothing ran during the capture: put the host bookkeeping back
+        for (size_t i = 0; i < local.size(); i++) { lat[local[i]]->capturing = false; lat[local[i]]->epoch = epoch0[i]; lat[local[i]]->iter = iter0; }
+        iter = iter0;
+        g.exec = exec; g.key = key; g.action = action;
+    }
+    for (int r : local)
+        if (tclb_dyn_set(lat[r]->dyn_dev(), iter, lat[r]->epoch, st) != 0) fail("graph replay: cannot set the iteration counters");
+    for (int p = 0; p < pairs; p++) TCLB_CUDA(cudaGraphLaunch((cudaGraphExec_t)g.exec, st));
+    iter += 2 * pairs;
+    for (int r : local) { lat[r]->iter = iter; lat[r]->epoch += g.launches * (unsigned)pairs; }
+    graph_replays += 2LL * pairs;
+}
+
 void Domain::iterate(int n, bool globals_on_last, bool globals_every) {
     int a = model->find_action("Iteration");
+    // iterations that need nothing from the host go through the captured graph, two at a time
+    if (!globals_every && n >= 8 && graph_possible(a)) {
+        const int plain = globals_on_last ? n - 1 : n;
+        const int pairs = plain / 2;
+        if (pairs > 0) { run_graph_pairs(a, pairs); n -= 2 * pairs; }
+    }
     for (int i = 0; i < n; i++) {
         bool g = globals_every || (globals_on_last && i == n - 1);
         run_action(a, g ? TCLB_GLOBALS_INTEGRATE : TCLB_GLOBALS_NONE);

@@ -69,6 +69,13 @@ class Lattice {
     HaloTarget halo[TCLB_MAX_NEIGH];
     void *stream;                  // cudaStream_t
     int block_x = 0, block_y = 0;
+    // CUDA-graph capture of the iteration loop (Domain::iterate): while `capturing`, launches read iteration/epoch from
+    // dyn_dev() plus the offsets recorded here; graph_version changes whenever a captured launch parameter changes
+    bool capturing = false;
+    int cap_iter_off = 0;
+    unsigned cap_epoch_base = 0;
+    unsigned long graph_version = 0;
+    int *dyn_dev() const { return dyn_dev_; }
     double origin[3] = {0.0, 0.0, 0.0};   // <Geometry px py pz>: node (i,j,k) sits at origin + (i,j,k) + 0.5
 
     // ---- memory access ----
@@ -136,6 +143,7 @@ class Lattice {
     void *cuts_dev_;
     void *st_dev_;
     int st_n_;
+    int *dyn_dev_ = nullptr;          // device int[2]: iteration and epoch at the start of a replayed graph
     void *particles_dev_ = nullptr;   // real_t[n_particles_][16]
     int n_particles_ = 0, particles_cap_ = 0;
     bool owns_stream_ = false;
@@ -172,6 +180,14 @@ class Domain {
     std::vector<int> local;                // ranks owned here
     int iter;
     bool use_direct_halo;                  // fused in-kernel halo (product path) vs copy exchange (baseline)
+    // The iteration loop as a CUDA graph: two iterations (one per snapshot orientation) are captured once and replayed;
+    // pays off when the lattice is small enough for launch latency to show.  Used by iterate() when nothing in the loop
+    // needs the host (no Globals, no particle stages, fused halo, one device in this process).
+    bool use_graphs = true;
+    long long graph_replays = 0;           // statistics: iterations executed through graph replays
+    bool graph_possible(int action) const;
+    void run_graph_pairs(int action, int pairs);
+    void drop_graphs();
     // hooks for multi-process operation
     std::function<void(int /*epoch*/)> exchange_hook;       // HALO_NONE: external (NCCL/gloo) exchange after every stage
     std::function<void(double *, int, int)> reduce_hook;    // (values, count, op) across processes
@@ -196,6 +212,12 @@ class Domain {
     std::vector<double> globals;           // reduced over all ranks
     void reduce_globals();
     long long nodes() const { return (long long)dec.tot[0] * dec.tot[1] * dec.tot[2]; }
+
+  private:
+    // one instantiated graph per snapshot orientation at entry (cur = 0 / 1)
+    struct GraphSlot { void *exec = nullptr; unsigned long key = 0; int action = -1; unsigned launches = 0; };
+    GraphSlot graph_[2];
+    unsigned long graph_key() const;
 };
 
 }  // namespace tclb

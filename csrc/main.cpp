@@ -41,6 +41,7 @@ int main(int argc, char **argv) {
         if (pos.size() >= 2) { pos.push_back(a); continue; }      // everything after the case file is an XPATH edit
         if (a == "--precision") opt.precision = need("--precision");
         else if (a == "--simplepart") opt.simplepart_config = need("--simplepart");
+        else if (a == "--no-graph") setenv("TCLB_NO_GRAPH", "1", 1);
         else if (a == "--cpu") opt.backend = TCLB_BACKEND_CPU;
         else if (a == "--gpu") opt.backend = TCLB_BACKEND_CUDA;
         else if (a == "--ranks") opt.nranks = atoi(need("--ranks").c_str());

@@ -51,6 +51,9 @@ int tclb_domain_get_quantity(tclb_domain_h *, int rank, const char *quantity, co
 int tclb_domain_color(tclb_domain_h *, int rank, int zplane, float scale, unsigned char *rgba);
 int tclb_domain_reset_average(tclb_domain_h *);
 int tclb_domain_set_block(tclb_domain_h *, int bx, int by);
+/* iterate() runs launch-only stretches of the loop as a replayed CUDA graph (default on for CUDA); statistics */
+int tclb_domain_use_graphs(tclb_domain_h *, int on);
+long long tclb_domain_graph_iterations(tclb_domain_h *);
 int tclb_domain_save_pri(tclb_domain_h *, int rank, const char *file);
 int tclb_domain_load_pri(tclb_domain_h *, int rank, const char *file);
 /* raw device views for DLPack/torch coupling: base pointer of the CURRENT snapshot of a rank and its shape

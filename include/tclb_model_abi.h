@@ -12,7 +12,7 @@
 extern "C" {
 #endif
 
-#define TCLB_ABI_VERSION 8
+#define TCLB_ABI_VERSION 9
 #define TCLB_MAX_NEIGH 9            /* (dy,dz) in {-1,0,1}^2 ; x is never decomposed */
 #define TCLB_MAX_RANKS 16           /* subdomains that exchange Globals through peer memory (one box) */
 #define TCLB_GL_RING 8              /* depth of the Globals publication ring */
@@ -88,6 +88,8 @@ typedef struct {
     int block_x, block_y;
     /* particles (later phases) */
     const void *particles; int n_particles;
+    /* CUDA-graph launches: device int[2] = {iteration, epoch} at the start of the graph + this launch's constant offsets */
+    const int *dyn; int dyn_iter_off; unsigned dyn_epoch_off;
 } tclb_launch_t;
 
 typedef struct {

@@ -310,8 +310,16 @@ struct KArgs {
     int st_n;
     real_t *particles;           // [n_particles][16]: r, pos, vel, angular velocity, force, moment (RFI layout)
     int n_particles;
+    // launches captured in a CUDA graph take iteration and halo epoch from device memory (dyn[0], dyn[1] = values at
+    // the start of the graph) plus a constant offset, so one instantiated graph can be replayed; NULL otherwise
+    const int *dyn;
+    int dyn_iter_off;
+    unsigned dyn_epoch_off;
     real_t settings[N_SETTINGS > 0 ? N_SETTINGS : 1];
 };
+TCLB_HD int k_iter(const KArgs &a) { return a.dyn ? a.dyn[0] + a.dyn_iter_off : a.iter; }
+TCLB_HD unsigned k_epoch(const KArgs &a) { return a.dyn ? (unsigned)a.dyn[1] + a.dyn_epoch_off : a.sig_epoch; }
+TCLB_HD int k_zone_index(const KArgs &a) { return (a.dyn && a.zone_len > 1) ? (a.dyn[0] + a.dyn_iter_off) % a.zone_len : a.zone_index; }
 """)
     # ---- macros visible to model code ----
     macros: List[tuple] = []
@@ -321,8 +329,8 @@ struct KArgs {
     M("X", "((real_t)(n_x + ka_.off_x) + ka_.pos_x)"); M("Y", "((real_t)(n_y + ka_.off_y) + ka_.pos_y)")
     M("Z", "((real_t)(n_z + ka_.off_z) + ka_.pos_z)")
     M("NodeType", "n_type")
-    M("Time", "(ka_.iter)")
-    M("average_iter", "(ka_.iter - ka_.reset_iter)")
+    M("Time", "(k_iter(ka_))")
+    M("average_iter", "(k_iter(ka_) - ka_.reset_iter)")
     # plain settings are const-reference members of the node (not macros: names like `z`, `T`, `dt` must not
     # rewrite `u.z` or a parameter called z); after inlining they fold into constant-bank operands
     # zonal settings are read where they are used (a load per node for values only boundary nodes need would
@@ -401,11 +409,12 @@ struct Node {
     A(r"""    }
     TCLB_HD real_t zone_setting(int s) const {
         // the table is tiny (time levels x settings x zones): 32-bit index arithmetic
-        return ka_.zone[(ka_.zone_index * N_ZONESETTINGS + s) * ka_.zone_stride + (int)(n_type >> ZONE_SHIFT)];
+        return ka_.zone[(k_zone_index(ka_) * N_ZONESETTINGS + s) * ka_.zone_stride + (int)(n_type >> ZONE_SHIFT)];
     }
     TCLB_HD real_t zone_setting_dt(int s) const {
-        int ip = ka_.zone_index + 1 < ka_.zone_len ? ka_.zone_index + 1 : 0;
-        int im = ka_.zone_index > 0 ? ka_.zone_index - 1 : ka_.zone_len - 1;
+        const int zi = k_zone_index(ka_);
+        int ip = zi + 1 < ka_.zone_len ? zi + 1 : 0;
+        int im = zi > 0 ? zi - 1 : ka_.zone_len - 1;
         int zn = n_type >> ZONE_SHIFT;
         return (ka_.zone[((long long)ip * N_ZONESETTINGS + s) * ka_.zone_stride + zn] -
                 ka_.zone[((long long)im * N_ZONESETTINGS + s) * ka_.zone_stride + zn]) * (real_t)0.5;
@@ -429,7 +438,7 @@ struct Node {
         vector_t v; v.x = 0; v.y = 0; v.z = 0;
         for (int i = 0; i < ka_.st_n; i++) {
             const tclb_st_mode_t &w = ka_.st[i];
-            real_t ph = (real_t)(w.k[0] * x + w.k[1] * y + w.k[2] * z + w.freq * (double)ka_.iter);
+            real_t ph = (real_t)(w.k[0] * x + w.k[1] * y + w.k[2] * z + w.freq * (double)k_iter(ka_));
             real_t s = sin(ph), c = cos(ph);
             v.x += (real_t)w.a[0] * c + (real_t)w.b[0] * s;
             v.y += (real_t)w.a[1] * c + (real_t)w.b[1] * s;

@@ -148,6 +148,8 @@ def core():
         "tclb_domain_color": [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p],
         "tclb_domain_reset_average": [C.c_void_p],
         "tclb_domain_set_block": [C.c_void_p, C.c_int, C.c_int],
+        "tclb_domain_use_graphs": [C.c_void_p, C.c_int],
+        "tclb_domain_graph_iterations": [C.c_void_p],
         "tclb_domain_save_pri": [C.c_void_p, C.c_int, C.c_char_p],
         "tclb_domain_load_pri": [C.c_void_p, C.c_int, C.c_char_p],
         "tclb_domain_snapshot_ptr": [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)],
@@ -303,6 +305,15 @@ class Domain:
 
     def set_halo_mode(self, direct: bool):
         _check(self.lib.tclb_domain_set_halo_mode(self.h, 1 if direct else 0))
+
+    def use_graphs(self, on: bool = True):
+        """run launch-only stretches of iterate() as a replayed CUDA graph (default on for CUDA domains)"""
+        _check(self.lib.tclb_domain_use_graphs(self.h, 1 if on else 0))
+
+    @property
+    def graph_iterations(self) -> int:
+        self.lib.tclb_domain_graph_iterations.restype = C.c_longlong
+        return int(self.lib.tclb_domain_graph_iterations(self.h))
 
     def set_block(self, bx: int, by: int = 0):
         _check(self.lib.tclb_domain_set_block(self.h, bx, by))

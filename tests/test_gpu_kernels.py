@@ -230,3 +230,28 @@ def test_gpu_particles_match_cpu_oracle(tclb_bin, tmp_path):
                 assert abs(float(x) - float(y)) <= 1e-9 * max(abs(float(x)), abs(float(y))) + 1e-12, (n, x, y)
     fx = [abs(float(r[8])) for r in out["gpu"][0][1:]]
     assert max(fx) > 1e-3                                   # the particles do exchange momentum with the fluid
+
+
+@pytest.mark.parametrize("model,shape,nranks", [("d2q9", (64, 40, 1), 1), ("d3q19", (32, 20, 16), 2), ("d3q27_cumulant", (32, 20, 16), 4)])
+def test_gpu_graph_replay_is_bitwise_identical(model, shape, nranks):
+    """iterate() replays a captured two-iteration CUDA graph (iteration number, halo epoch and the time index of zonal
+    series come from device memory): results equal the plain launch loop bit for bit, also after a setting changes"""
+    from helpers import setup_case
+    from tclb_b200.runtime import Domain, Model
+    m = Model(model, "float")
+    out = []
+    for graphs in (True, False):
+        d = Domain(m, shape, "cuda", nranks=nranks)
+        d.use_graphs(graphs)
+        setup_case(d, m, shape)
+        zs = [z for z in m.zonesettings if not z.endswith("InObj")]
+        if zs:
+            d.set_zone_series(zs[0], 0, [0.01 + 0.001 * k for k in range(7)])  # time-dependent zonal setting
+        d.iterate(41)
+        d.set_setting(m.settings[0], d.get_setting(m.settings[0]) * 1.01)      # invalidates the captured parameters
+        d.iterate(30, globals_on_last=True)
+        out.append(({f: d.get_field(f) for f in m.fields[:5]}, d.globals(), d.graph_iterations, d.iter))
+    assert out[0][2] >= 60 and out[1][2] == 0 and out[0][3] == out[1][3] == 71
+    for f in out[0][0]:
+        assert np.array_equal(out[0][0][f], out[1][0][f]), f
+    assert out[0][1] == out[1][1]
