@@ -7,8 +7,22 @@
 #include <cstdlib>
 #include <cstring>
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 namespace tclb {
+
+const DebugFlags &debug_flags() {
+    static const DebugFlags f = [] {
+        DebugFlags d;
+        if (const char *e = getenv("TCLB_DEBUG")) {
+            d.sync = strstr(e, "sync") != nullptr;
+            d.poison = strstr(e, "poison") != nullptr;
+        }
+        if (const char *p = getenv("TCLB_PROFILE")) d.profile = p[0] && p[0] != '0';
+        return d;
+    }();
+    return f;
+}
 
 Box Box::intersect(const Box &o) const {
     Box r;
@@ -165,6 +179,33 @@ void Lattice::get_particles(std::vector<double> &rows) {
         to_host(f.data(), particles_dev_, f.size() * 4);
         for (size_t i = 0; i < f.size(); i++) rows[i] = f[i];
     } else to_host(rows.data(), particles_dev_, rows.size() * 8);
+}
+// debug aid: every ghost value of `snap` becomes NaN (all-ones bytes are a NaN in half, float and double)
+void Lattice::poison_ghosts(int snap, int stage) {
+    const size_t ss = model->storage_size(), row = (size_t)nx * ss, plane = (size_t)NY * row;
+    const unsigned char *saved = model->d->stages[stage].save_field;
+    for (int f = 0; f < model->d->n_fields; f++) {
+        if (saved && !saved[f]) continue;
+        char *base = (char *)field_ptr(snap, f);
+        if (backend == TCLB_BACKEND_CUDA) {
+            TCLB_CUDA(cudaSetDevice(device));
+            cudaStream_t st = (cudaStream_t)stream;
+            if (gz > 0) {
+                TCLB_CUDA(cudaMemsetAsync(base, 0xFF, (size_t)gz * plane, st));
+                TCLB_CUDA(cudaMemsetAsync(base + (size_t)(nz + gz) * plane, 0xFF, (size_t)gz * plane, st));
+            }
+            if (gy > 0) {
+                TCLB_CUDA(cudaMemset2DAsync(base + (size_t)gz * plane, plane, 0xFF, (size_t)gy * row, nz, st));
+                TCLB_CUDA(cudaMemset2DAsync(base + (size_t)gz * plane + (size_t)(ny + gy) * row, plane, 0xFF, (size_t)gy * row, nz, st));
+            }
+        } else {
+            if (gz > 0) { memset(base, 0xFF, (size_t)gz * plane); memset(base + (size_t)(nz + gz) * plane, 0xFF, (size_t)gz * plane); }
+            for (int z = 0; z < nz && gy > 0; z++) {
+                memset(base + (size_t)(z + gz) * plane, 0xFF, (size_t)gy * row);
+                memset(base + (size_t)(z + gz) * plane + (size_t)(ny + gy) * row, 0xFF, (size_t)gy * row);
+            }
+        }
+    }
 }
 void *Lattice::field_ptr(int snap, int field) const {
     return (char *)snap_[snap] + (size_t)field * plane_elems * model->storage_size();
@@ -450,7 +491,33 @@ void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode, bool
         }
     }
     if (backend == TCLB_BACKEND_CUDA) TCLB_CUDA(cudaSetDevice(device));
-    if (model->d->run_stage(stage, &L) != 0) fail("stage %s failed: %s", model->d->stages[stage].name, model->d->last_error());
+    // ---- observability / debugging switches (TCLB_DEBUG=sync,poison  TCLB_PROFILE=1) ----
+    const DebugFlags &dbg = debug_flags();
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    const bool timed = dbg.profile && backend == TCLB_BACKEND_CUDA && !capturing;
+    if (timed) {
+        TCLB_CUDA(cudaEventCreate(&ev0)); TCLB_CUDA(cudaEventCreate(&ev1));
+        TCLB_CUDA(cudaEventRecord(ev0, (cudaStream_t)stream));
+    }
+    nvtxRangePushA(model->d->stages[stage].name);
+    const int rc = model->d->run_stage(stage, &L);
+    nvtxRangePop();
+    if (rc != 0) fail("stage %s failed: %s", model->d->stages[stage].name, model->d->last_error());
+    if (timed) {
+        TCLB_CUDA(cudaEventRecord(ev1, (cudaStream_t)stream));
+        TCLB_CUDA(cudaEventSynchronize(ev1));
+        float ms = 0;
+        TCLB_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+        cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+        StageStat &s = stage_stats[{stage, gmode}];
+        s.launches++; s.ms += ms;
+    }
+    if (dbg.sync && backend == TCLB_BACKEND_CUDA && !capturing) {
+        // like the reference's --enable-debug CROSS_SYNC: every launch is followed by a device sync and an error check
+        cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) fail("stage %s: %s", model->d->stages[stage].name, cudaGetErrorString(e));
+    }
 }
 void Lattice::clear_globals() {
     const int ng = model->d->n_globals;
@@ -733,6 +800,13 @@ void Domain::run_action(int action, int gmode) {
     for (int s = 0; s < a.n_stages; s++) {
         int in = s == 0 ? tab0 : tab1;
         if (s == first_particle && particles_in_hook) particles_in_hook();
+        // debug: NaN in the ghosts that this stage is about to fill (only safe when every writer runs after this point:
+        // all subdomains in this process on one stream, and the stage does not work in place)
+        if (debug_flags().poison && in != tab1 && (int)local.size() == dec.nranks && !lat[local[0]]->capturing) {
+            bool one_stream = true;
+            for (int r : local) one_stream = one_stream && (backend != TCLB_BACKEND_CUDA || lat[r]->stream == lat[local[0]]->stream);
+            if (one_stream) for (int r : local) lat[r]->poison_ghosts(tab1, a.stages[s]);
+        }
         for (int r : local) lat[r]->launch_stage(a.stages[s], in, tab1, gmode, s == a.n_stages - 1);
         if (s == last_particle && particles_out_hook) particles_out_hook();
         bool need_copy = false;
@@ -767,6 +841,7 @@ unsigned long Domain::graph_key() const {
 }
 bool Domain::graph_possible(int action) const {
     if (!use_graphs || backend != TCLB_BACKEND_CUDA || local.empty() || getenv("TCLB_NO_GRAPH")) return false;
+    if (debug_flags().profile || debug_flags().sync || debug_flags().poison) return false;   // per-launch instrumentation
     const tclb_action_t &a = model->d->actions[action];
     for (int s = 0; s < a.n_stages; s++) if (model->d->stages[a.stages[s]].particle) return false;
     for (int r : local) {

@@ -12,6 +12,7 @@
 #pragma once
 #include <cstdint>
 #include <functional>
+#include <map>
 #include <string>
 #include <vector>
 #include "arena.h"
@@ -26,6 +27,10 @@ struct Box {
     Box intersect(const Box &o) const;
     bool empty() const { return nx <= 0 || ny <= 0 || nz <= 0; }
 };
+
+// run-time switches read once from the environment: TCLB_DEBUG=sync,poison  TCLB_PROFILE=1
+struct DebugFlags { bool sync = false, poison = false, profile = false; };
+const DebugFlags &debug_flags();
 
 // what a rank knows about another rank's memory (own process: plain pointers; other process:
 // pointers obtained from a CUDA IPC mapping of that rank's arena)
@@ -106,6 +111,12 @@ class Lattice {
     void set_setting(int idx, double v);                   // applies derived-settings chain
     double get_setting(int idx) const { return settings[idx]; }
     void set_synthetic_turbulence(const std::vector<tclb_st_mode_t> &modes);
+    // ---- observability: TCLB_PROFILE=1 times every stage launch with CUDA events (device time,
+    // serialising), TCLB_DEBUG=sync checks for errors after every launch, TCLB_DEBUG=poison fills the ghost layers of
+    // the output snapshot with NaN before each stage so a missing halo write shows up as NaN instead of stale data
+    struct StageStat { long long launches = 0; double ms = 0; };
+    std::map<std::pair<int, int>, StageStat> stage_stats;   // (stage, globals mode) -> device time
+    void poison_ghosts(int snap, int stage);     // ghosts of the fields that `stage` saves
     // ---- particles (reference Lattice::CopyInParticles/CopyOutParticles, src/Lattice.cu.Rt:392-437) ----
     // rows of 16 doubles in the RFI layout (r, pos, vel, angular velocity, force, moment); forces start at zero
     void set_particles(const std::vector<double> &rows16);

@@ -575,6 +575,18 @@ int Solver::run() {
     h.reset();
     domain->sync();
     if (integrator) { integrator->finish(); integrator.reset(); domain->particles_in_hook = nullptr; domain->particles_out_hook = nullptr; }
+    if (debug_flags().profile) {
+        // per-stage device time (TCLB_PROFILE=1): CUDA events around every launch of the first local subdomain
+        Lattice *l = domain->lat[domain->local[0]];
+        static const char *gm[] = {"", "+Globals", "+Objective", "+Globals+Objective"};
+        logf(L_NOTICE_IMP, "%-32s %10s %12s %12s %10s", "stage", "launches", "total ms", "ms/launch", "GB/s");
+        const double bytes = (double)l->nx * l->ny * l->nz * model->bytes_per_update();
+        for (auto &kv : l->stage_stats) {
+            const double per = kv.second.ms / std::max<long long>(1, kv.second.launches);
+            logf(L_NOTICE_IMP, "%-32s %10lld %12.3f %12.5f %10.1f", (std::string(model->d->stages[kv.first.first].name) + gm[kv.first.second & 3]).c_str(),
+                 kv.second.launches, kv.second.ms, per, per > 0 ? bytes / (per * 1e-3) / 1e9 : 0.0);
+        }
+    }
     if (is_root()) {
         double d = walltime();
         logf(L_OUTPUT, "Total duration: %lf s = %lf min = %lf h", d, d / 60, d / 3600);

@@ -136,3 +136,23 @@ def test_objective_weights_switch_on_with_zone_settings():
     d.set_setting("FluxInObj", 0.0)
     d.iterate(1, globals_every=True)
     assert d.globals()["Objective"] == 0.0
+
+
+def test_debug_poison_mode_leaves_results_unchanged():
+    """TCLB_DEBUG=poison fills the ghost layers a stage is about to receive with NaN: with a complete halo exchange the
+    results are bit-identical, so any NaN in this mode points at a missing ghost write"""
+    import os
+    import subprocess
+    import sys
+    code = ("import sys; sys.path.insert(0, 'tests'); import numpy as np; from helpers import run_case;"
+            "r = run_case('d3q19', 'double', 'cpu', (32, 20, 16), 12, nranks=4);"
+            "print(repr(float(np.abs(r['U']).sum())), bool(np.isfinite(r['U']).all()))")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for env in ({}, {"TCLB_DEBUG": "poison,sync"}):
+        e = dict(os.environ)
+        e.update(env)
+        r = subprocess.run([sys.executable, "-c", code], cwd=root, env=e, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r.stdout.strip().split("\n")[-1])
+    assert outs[0] == outs[1] and outs[0].endswith("True"), outs
