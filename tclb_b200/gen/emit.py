@@ -317,9 +317,14 @@ struct KArgs {
     unsigned dyn_epoch_off;
     real_t settings[N_SETTINGS > 0 ? N_SETTINGS : 1];
 };
-TCLB_HD int k_iter(const KArgs &a) { return a.dyn ? a.dyn[0] + a.dyn_iter_off : a.iter; }
-TCLB_HD unsigned k_epoch(const KArgs &a) { return a.dyn ? (unsigned)a.dyn[1] + a.dyn_epoch_off : a.sig_epoch; }
-TCLB_HD int k_zone_index(const KArgs &a) { return (a.dyn && a.zone_len > 1) ? (a.dyn[0] + a.dyn_iter_off) % a.zone_len : a.zone_index; }
+// Kernel variant bit 4 (GMODE & 4) = "launched from a captured graph": only that variant reads the device-resident
+// counters.  Keeping the run-time test out of the ordinary variants matters: with it the d3q27_cumulant kernel
+// lost 4 % (same instruction count, different schedule) - measured on B200.
+template <int GMODE> TCLB_HD int k_iter(const KArgs &a) { return (GMODE & 4) ? a.dyn[0] + a.dyn_iter_off : a.iter; }
+template <int GMODE> TCLB_HD unsigned k_epoch(const KArgs &a) { return (GMODE & 4) ? (unsigned)a.dyn[1] + a.dyn_epoch_off : a.sig_epoch; }
+template <int GMODE> TCLB_HD int k_zone_index(const KArgs &a) {
+    return ((GMODE & 4) && a.zone_len > 1) ? (a.dyn[0] + a.dyn_iter_off) % a.zone_len : a.zone_index;
+}
 """)
     # ---- macros visible to model code ----
     macros: List[tuple] = []
@@ -329,8 +334,8 @@ TCLB_HD int k_zone_index(const KArgs &a) { return (a.dyn && a.zone_len > 1) ? (a
     M("X", "((real_t)(n_x + ka_.off_x) + ka_.pos_x)"); M("Y", "((real_t)(n_y + ka_.off_y) + ka_.pos_y)")
     M("Z", "((real_t)(n_z + ka_.off_z) + ka_.pos_z)")
     M("NodeType", "n_type")
-    M("Time", "(k_iter(ka_))")
-    M("average_iter", "(k_iter(ka_) - ka_.reset_iter)")
+    M("Time", "(k_iter<GMODE>(ka_))")
+    M("average_iter", "(k_iter<GMODE>(ka_) - ka_.reset_iter)")
     # plain settings are const-reference members of the node (not macros: names like `z`, `T`, `dt` must not
     # rewrite `u.z` or a parameter called z); after inlining they fold into constant-bank operands
     # zonal settings are read where they are used (a load per node for values only boundary nodes need would
@@ -402,17 +407,17 @@ struct Node {
         n_type = ka_.flags[n_idx];
         if (GMODE & 1) {
             for (int i = 0; i < N_GLOBALS; i++) gacc_[i * GSTRIDE] = (i >= SUM_GLOBALS) ? (real_t)-1e30 : (real_t)0;
-        } else if (GMODE == 2) gacc_[0] = 0;""")
+        } else if ((GMODE & 3) == 2) gacc_[0] = 0;""")
     for i, s in enumerate(m.zonesettings):
         if s.name in member_zs:
             A(f"        {s.name} = zone_setting({i});")
     A(r"""    }
     TCLB_HD real_t zone_setting(int s) const {
         // the table is tiny (time levels x settings x zones): 32-bit index arithmetic
-        return ka_.zone[(k_zone_index(ka_) * N_ZONESETTINGS + s) * ka_.zone_stride + (int)(n_type >> ZONE_SHIFT)];
+        return ka_.zone[(k_zone_index<GMODE>(ka_) * N_ZONESETTINGS + s) * ka_.zone_stride + (int)(n_type >> ZONE_SHIFT)];
     }
     TCLB_HD real_t zone_setting_dt(int s) const {
-        const int zi = k_zone_index(ka_);
+        const int zi = k_zone_index<GMODE>(ka_);
         int ip = zi + 1 < ka_.zone_len ? zi + 1 : 0;
         int im = zi > 0 ? zi - 1 : ka_.zone_len - 1;
         int zn = n_type >> ZONE_SHIFT;
@@ -438,7 +443,7 @@ struct Node {
         vector_t v; v.x = 0; v.y = 0; v.z = 0;
         for (int i = 0; i < ka_.st_n; i++) {
             const tclb_st_mode_t &w = ka_.st[i];
-            real_t ph = (real_t)(w.k[0] * x + w.k[1] * y + w.k[2] * z + w.freq * (double)k_iter(ka_));
+            real_t ph = (real_t)(w.k[0] * x + w.k[1] * y + w.k[2] * z + w.freq * (double)k_iter<GMODE>(ka_));
             real_t s = sin(ph), c = cos(ph);
             v.x += (real_t)w.a[0] * c + (real_t)w.b[0] * s;
             v.y += (real_t)w.a[1] * c + (real_t)w.b[1] * s;
@@ -557,11 +562,13 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     A("int run_stage_impl(int stage, const tclb_launch_t *L) {")
     A("    KArgs a; int bx, by; fill_args(a, L, bx, by);")
     A("    // kernel variant: 0 none, 1 all Globals, 2 Objective weights only, 3 all Globals + Objective weights")
-    A("    const int gm = L->globals_mode == TCLB_GLOBALS_INTEGRATE ? (L->obj_enabled ? 3 : 1) : L->globals_mode;")
-    A("    switch (stage * 4 + gm) {")
+    A("    // 4 = no Globals, iteration/epoch from device memory (launches captured in a CUDA graph)")
+    A("    int gm = L->globals_mode == TCLB_GLOBALS_INTEGRATE ? (L->obj_enabled ? 3 : 1) : L->globals_mode;")
+    A('    if (L->dyn) { if (gm != 0) { set_error("graph launches carry no Globals"); return -1; } gm = 4; }')
+    A("    switch (stage * 8 + gm) {")
     for si in range(len(m.stages)):
-        for gm in range(4):
-            A(f"    case {si * 4 + gm}: return launch_stage<{si}, {gm}>(a, L, bx, by);")
+        for gm in range(5):
+            A(f"    case {si * 8 + gm}: return launch_stage<{si}, {gm}>(a, L, bx, by);")
     A('    default: set_error("bad stage/globals mode"); return -1;')
     A("    }\n}")
     A("int get_quantity_impl(int q, const tclb_launch_t *L) {")
