@@ -844,6 +844,11 @@ bool Domain::graph_possible(int action) const {
     if (debug_flags().profile || debug_flags().sync || debug_flags().poison) return false;   // per-launch instrumentation
     const tclb_action_t &a = model->d->actions[action];
     for (int s = 0; s < a.n_stages; s++) if (model->d->stages[a.stages[s]].particle) return false;
+    // launch latency only shows on small lattices; on large ones the graph variant of the kernels (which reads its
+    // counters from memory) is a few percent slower than the plain one - measured - so the plain loop stays
+    long long nodes = 0;
+    for (int r : local) nodes += (long long)lat[r]->nx * lat[r]->ny * lat[r]->nz;
+    if (nodes > (1ll << 22) && !getenv("TCLB_FORCE_GRAPH")) return false;
     for (int r : local) {
         const Lattice *l = lat[r];
         if (l->halo_mode != TCLB_HALO_DIRECT) return false;                    // the copy/NCCL exchange runs on the host

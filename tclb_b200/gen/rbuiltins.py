@@ -713,9 +713,23 @@ def install_poly(I):
         pos = np.nonzero(idx)[0] if idx.dtype == bool else (idx.astype(int) - 1)
         for j, p_ in enumerate(pos.tolist()):
             flat[p_] = vals.ravel()[j % vals.size]
-        return flat.reshape(x.shape, order="F")
+        out = flat.reshape(x.shape, order="F")
+        cn = getattr(a[0], "colnames", None)
+        if cn and out.ndim == 2:
+            from .rinterp import NamedMat
+            out = NamedMat(out, cn)
+        return out
     G.set("replace", _replace)
-    G.set("provideDimnames", lambda I, a, k: a[0])
+    def _provide_dimnames(I, a, k):
+        from .rinterp import NamedMat
+        base = k.get("base", a[1] if len(a) > 1 else None)
+        if isinstance(base, RList) and len(base) >= 2 and vec(a[0]).ndim == 2:
+            cn = [to_str(v) for v in vec(list(base.values())[1]).tolist()]
+            m = vec(a[0])
+            return NamedMat(m, (cn * (m.shape[1] // max(1, len(cn)) + 1))[:m.shape[1]])
+        return a[0]
+    G.set("provideDimnames", _provide_dimnames)
+    G.set("as.data.frame", lambda I, a, k: I.call(G.get("data.frame"), [a[0]], OrderedDict()))
     G.set("deriv", lambda I, a, k: (_ for _ in ()).throw(RError("deriv() of symbolic expressions is not supported by this front-end")))
     G.set("c_header", lambda I, a, k: NULL)
     G.set("c_table_decl", lambda I, a, k: a[0])

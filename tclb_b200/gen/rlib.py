@@ -255,7 +255,47 @@ def install_boundary(I, env):
         return NULL
 
     def zouhe_new(I_, a, k):
-        raise RError("ZouHeNew is not available in this front-end")
+        """ZouHeNew(EQ, f, direction, sign, order, group=f, known="rho", mom): the unknown populations become the
+        bounced non-equilibrium closure, the moments up to `order` are matched and the equations are solved one
+        unknown at a time (reference src/lib/boundary.R:118-150)."""
+        g = _args(["EQ", "f", "direction", "sign", "order", "group", "known", "mom"], a, k)
+        eq = eq_from(g["EQ"])
+        f = _pvec(g["f"])
+        fs = _pvec(g["group"]) if "group" in g else f
+        direction, sign, order = int(scalar(g["direction"])), int(scalar(g["sign"])), int(scalar(g["order"]))
+        U = np.asarray(eq.U).astype(int)
+        bounce = lbmlib.bounce_index(U)
+        sel = sign * U[:, direction - 1] > 0
+        feq = eq.feq
+        new = fs.copy()
+        for i in np.nonzero(sel)[0]:
+            new[int(i)] = feq[int(i)] + (fs[int(bounce[i])] - feq[int(bounce[i])])
+        Rs = new @ np.asarray(eq.mat, dtype=float)
+        low = [i for i in range(len(eq.order)) if eq.order[i] <= order]
+        mom = _pvec(g["mom"]) if "mom" in g else None
+        eqs = [(mom[j] if mom is not None else eq.Req[i]) - Rs[i] for j, i in enumerate(low)]
+        known = set(str(v) for v in vec(g["known"]).tolist()) if "known" in g else {"rho"}
+        known |= {to_c(f[int(i)]) for i in np.nonzero(~sel)[0]}
+        needed = []
+        for p in new:
+            for sy in p.symbols():
+                if sy not in known and sy not in needed:
+                    needed.append(sy)
+        while needed:
+            pick = None
+            for e_i, e in enumerate(eqs):
+                present = [sy for sy in needed if sy in e.symbols()]
+                if len(present) == 1:
+                    pick = (e_i, present[0])
+                    break
+            if pick is None:
+                raise RError("Cannot solve the boundary problem in ZouHe")
+            e_i, sy = pick
+            _c_pull(I_, eqs[e_i], sy)
+            needed.remove(sy)
+            eqs.pop(e_i)
+        _emit(I_, c_assign([f[int(i)] for i in np.nonzero(sel)[0]], [new[int(i)] for i in np.nonzero(sel)[0]], indent="", optimize=False))
+        return NULL
 
     env.set("Bounce", bounce)
     env.set("FullBounceBack", full_bounce_back)
