@@ -650,6 +650,11 @@ def install_poly(I):
             I.out.append((sep if "sep" in k else ", ").join(items) if len(items) > 1 else items[0])
             return NULL
         lhs, rhs = a[0], a[1]
+        if (isinstance(lhs, PVec) and isinstance(rhs, PVec) and len(lhs) == len(rhs) >= 2 and not getattr(I, "plain_c", False)
+                and eq in ("=", "+=", "-=") and all(len(p.t) == 1 for p in lhs)):
+            # symbolic block: same rewriting as the native models get (one reciprocal per divisor, shared products)
+            I.out.append(c_assign([to_c(p) for p in lhs], list(rhs), op=eq, indent=""))
+            return NULL
         L = [to_c(p) for p in lhs] if isinstance(lhs, PVec) else [to_c(lhs)] if isinstance(lhs, Poly) else [to_str(v) for v in vec(lhs).tolist()]
         if isinstance(rhs, PVec):
             R = [to_c(p) for p in rhs]
