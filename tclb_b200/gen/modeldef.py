@@ -391,6 +391,9 @@ class ModelDef:
                 if self.permissive_access or f.read.get(s.name) is None:
                     f.read[s.name] = True
         self._pack_nodetypes()
+        if not self.adjoint:
+            # the reference compiles adjoint quantities only under #ifdef ADJOINT (src/LatticeContainer.inc.cpp.Rt:429)
+            self.quantities = [q for q in self.quantities if not q.adjoint]
         # adjoint auto settings / globals
         if self.adjoint == 1:
             for s in list(self.settings):

@@ -715,7 +715,7 @@ def install_poly(I):
         idx = vec(a[1])
         vals = vec(a[2])
         flat = x.ravel(order="F")
-        pos = np.nonzero(idx)[0] if idx.dtype == bool else (idx.astype(int) - 1)
+        pos = np.nonzero(idx.ravel(order="F"))[0] if idx.dtype == bool else (idx.astype(int) - 1)
         for j, p_ in enumerate(pos.tolist()):
             flat[p_] = vals.ravel()[j % vals.size]
         out = flat.reshape(x.shape, order="F")

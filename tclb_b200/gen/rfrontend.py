@@ -228,6 +228,8 @@ def load_dynamics_r(model_dir: str, name: Optional[str] = None, options: Optiona
     I.source_hooks["conf.R"] = lambda I_, e: NULL
     from . import rlib
     rlib.install(I)
+    for scope in (I.globals, env):
+        I.builtins.update({k: v for k, v in scope.vars.items() if callable(v)})
     path = os.path.join(model_dir, "Dynamics.R")
     I.run(open(path).read(), env)
     if finalize:

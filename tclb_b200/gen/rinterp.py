@@ -124,9 +124,12 @@ class Interp:
         self.include_dirs = list(include_dirs or [])
         self.out: List[str] = []          # captured cat()/print output (template engine reads it)
         self.sourced: List[str] = []
+        # TCLB_PLAIN_C=1: emit C() blocks as written (no reciprocal / shared-product rewriting), for A/B measurements
+        self.plain_c = bool(os.environ.get("TCLB_PLAIN_C"))
         self.source_hooks: Dict[str, Callable] = {}
         from .rbuiltins import install
         install(self)
+        self.builtins: Dict[str, Any] = dict(self.globals.vars)   # functions stay reachable when a variable takes their name
 
     # ---- public ----
     def run(self, src: str, env: Optional[Env] = None):
@@ -366,6 +369,15 @@ class Interp:
             if fn is None:
                 raise RError(f"could not find function \"{fname}\"")
             fn = self.force(fn)
+            if not callable(fn) and not isinstance(fn, Closure):
+                # R looks for a FUNCTION of that name: a variable `C` (a density called C) does not hide C()
+                e, fn2 = env, None
+                while e is not None and fn2 is None:
+                    v = e.vars.get(fname)
+                    if v is not None and (callable(v) or isinstance(v, Closure)):
+                        fn2 = v
+                    e = e.parent
+                fn = fn2 or self.builtins.get(fname) or fn
         else:
             fn = self.eval(fnode, env)
         pos, kw = self.eval_args(args, env)
