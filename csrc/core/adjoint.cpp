@@ -1,0 +1,173 @@
+#include "adjoint.h"
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <cstdlib>
+#include <cstring>
+#include "common.h"
+
+extern "C" int tclb_adjoint_fold_ghosts(void *adj, int real_size, int on_device, int nfields, int nx, int ny, int nz, int gy, int gz,
+                                        void *stream);
+
+namespace tclb {
+
+#define ADJ_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) fail("adjoint: %s", cudaGetErrorString(e__)); } while (0)
+
+Adjoint::Adjoint(Domain *dom) : dom_(dom), lat_(nullptr) {
+    if (dom->dec.nranks != 1 || dom->local.size() != 1)
+        fail("adjoint: this version handles one subdomain (got %d ranks)", dom->dec.nranks);
+    lat_ = dom->lat[dom->local[0]];
+    Model *m = dom->model;
+    if (m->storage_size() != m->real_size()) fail("adjoint: needs plain float/double lattice storage");
+    action_ = m->find_action("Iteration");
+    if (action_ < 0) fail("adjoint: model has no Iteration action");
+    const tclb_action_t &a = m->d->actions[action_];
+    if (a.n_stages != 1) fail("adjoint: action Iteration of %s has %d stages; only single-stage actions are differentiated", m->d->name, a.n_stages);
+    stage_ = a.stages[0];
+    for (int f = 0; f < m->d->n_fields; f++)
+        if (!m->d->stages[stage_].save_field[f]) fail("adjoint: stage %s does not save field %s", m->d->stages[stage_].name, m->d->fields[f].name);
+    // companion library: <primal>.so -> <primal>_ad.so
+    std::string p = m->path;
+    const size_t dot = p.rfind(".so");
+    if (dot == std::string::npos) fail("adjoint: cannot derive the adjoint library name from %s", p.c_str());
+    p = p.substr(0, dot) + "_ad.so";
+    lib_ = dlopen(p.c_str(), RTLD_NOW | RTLD_LOCAL);
+    if (!lib_) fail("adjoint: cannot load %s (%s); build it with tclb_b200.build.build_adjoint_lib", p.c_str(), dlerror());
+    fn_ = (stage_fn)dlsym(lib_, "tclb_model_adjoint_stage");
+    err_ = (err_fn)dlsym(lib_, "tclb_model_adjoint_error");
+    typedef int (*info_fn)(int *, int *, int *);
+    info_fn info = (info_fn)dlsym(lib_, "tclb_model_adjoint_info");
+    if (!fn_ || !err_ || !info) fail("adjoint: %s does not export the adjoint entry points", p.c_str());
+    int rs = 0, dirs = 0, nf = 0;
+    if (info(&rs, &dirs, &nf) != TCLB_ABI_VERSION) fail("adjoint: %s was built for another ABI version (rebuild it)", p.c_str());
+    if (rs != m->real_size() || nf != m->d->n_fields) fail("adjoint: %s does not match the primal library", p.c_str());
+    rs_ = rs;
+    bytes_ = (size_t)m->d->n_fields * lat_->plane_elems * rs_;
+    const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+    for (int i = 0; i < 2; i++) { adj_[i] = alloc(bytes_, dev); fill_zero(adj_[i]); }
+    const char *cap = getenv("TCLB_TAPE_DEVICE_BYTES");
+    dev_tape_cap_ = cap ? (size_t)atoll(cap) : ((size_t)8 << 30);
+}
+Adjoint::~Adjoint() {
+    drop_tape();
+    const bool dev = lat_ && lat_->backend == TCLB_BACKEND_CUDA;
+    for (int i = 0; i < 2; i++) if (adj_[i]) release(adj_[i], dev);
+    if (lib_) dlclose(lib_);
+}
+void *Adjoint::alloc(size_t bytes, bool device) const {
+    void *p = nullptr;
+    if (device) { ADJ_CUDA(cudaSetDevice(lat_->device)); ADJ_CUDA(cudaMalloc(&p, bytes)); }
+    else { p = malloc(bytes); if (!p) fail("adjoint: out of host memory (%zu bytes)", bytes); }
+    return p;
+}
+void Adjoint::release(void *p, bool device) const {
+    if (device) cudaFree(p); else free(p);
+}
+void Adjoint::fill_zero(void *p) const {
+    if (lat_->backend == TCLB_BACKEND_CUDA) ADJ_CUDA(cudaMemsetAsync(p, 0, bytes_, (cudaStream_t)lat_->stream));
+    else memset(p, 0, bytes_);
+}
+void Adjoint::zero() { fill_zero(adj_[0]); fill_zero(adj_[1]); }
+void Adjoint::drop_tape() {
+    for (Frame &f : tape_) release(f.data, f.on_device);
+    tape_.clear();
+    dev_tape_bytes_ = 0;
+}
+void Adjoint::record(int n) {
+    const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+    const int obj = dom_->model->find_global("Objective");
+    for (int i = 0; i < n; i++) {
+        Frame f;
+        f.iter = lat_->iter;
+        f.on_device = dev && dev_tape_bytes_ + lat_->snap_bytes <= dev_tape_cap_;
+        f.data = alloc(lat_->snap_bytes, f.on_device);
+        const void *src = lat_->snap_ptr(lat_->cur);
+        if (dev) {
+            ADJ_CUDA(cudaMemcpyAsync(f.data, src, lat_->snap_bytes, f.on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost,
+                                     (cudaStream_t)lat_->stream));
+            if (!f.on_device) ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
+            else dev_tape_bytes_ += lat_->snap_bytes;
+        } else memcpy(f.data, src, lat_->snap_bytes);
+        tape_.push_back(f);
+        dom_->iterate(1, false, true);
+        if (obj >= 0) objective += dom_->globals[obj];
+    }
+}
+void Adjoint::step(const void *primal_in, int iter) {
+    lat_->upload_zone_table_if_dirty();
+    tclb_launch_t L;
+    lat_->fill_launch(L);
+    L.snap_in = const_cast<void *>(primal_in);
+    L.snap_out = nullptr;
+    L.iter = iter;
+    L.zone_index = L.zone_len > 1 ? iter % L.zone_len : 0;
+    L.globals_mode = TCLB_GLOBALS_NONE;
+    L.halo_mode = TCLB_HALO_NONE;
+    L.obj_enabled = 1;
+    void *out = adj_[cur_], *in = adj_[cur_ ^ 1];
+    fill_zero(in);
+    if (lat_->backend == TCLB_BACKEND_CUDA) ADJ_CUDA(cudaSetDevice(lat_->device));
+    if (fn_(stage_, &L, out, in) != 0) fail("adjoint stage failed: %s", err_());
+    if (tclb_adjoint_fold_ghosts(in, rs_, lat_->backend == TCLB_BACKEND_CUDA, dom_->model->d->n_fields, lat_->nx, lat_->ny, lat_->nz,
+                                 lat_->gy, lat_->gz, lat_->stream) != 0)
+        fail("adjoint: ghost fold failed");
+    cur_ ^= 1;
+}
+void Adjoint::reverse() {
+    const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+    void *stage_buf = nullptr;
+    while (!tape_.empty()) {
+        Frame f = tape_.back();
+        tape_.pop_back();
+        const void *src = f.data;
+        if (dev && !f.on_device) {
+            if (!stage_buf) stage_buf = alloc(lat_->snap_bytes, true);
+            ADJ_CUDA(cudaMemcpyAsync(stage_buf, f.data, lat_->snap_bytes, cudaMemcpyHostToDevice, (cudaStream_t)lat_->stream));
+            src = stage_buf;
+        }
+        step(src, f.iter);
+        if (dev) ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
+        release(f.data, f.on_device);
+        if (f.on_device) dev_tape_bytes_ -= lat_->snap_bytes;
+    }
+    if (stage_buf) release(stage_buf, true);
+}
+void Adjoint::steady(int n) {
+    for (int i = 0; i < n; i++) step(lat_->snap_ptr(lat_->cur), lat_->iter);
+    if (lat_->backend == TCLB_BACKEND_CUDA) ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
+}
+// interior <-> dense copies (adjoint buffers have the snapshot layout [field][NZ][NY][nx] in real_t)
+void Adjoint::get_field(int field, void *dst) const {
+    const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+    const size_t row = (size_t)lat_->nx * rs_;
+    const char *base = (const char *)adj_[cur_] + (size_t)field * lat_->plane_elems * rs_;
+    if (dev) ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
+    for (int z = 0; z < lat_->nz; z++) {
+        const char *src = base + ((size_t)(z + lat_->gz) * lat_->NY + lat_->gy) * row;
+        char *d = (char *)dst + (size_t)z * lat_->ny * row;
+        if (dev) ADJ_CUDA(cudaMemcpy2D(d, row, src, row, row, lat_->ny, cudaMemcpyDeviceToHost));
+        else for (int y = 0; y < lat_->ny; y++) memcpy(d + y * row, src + y * row, row);
+    }
+}
+void Adjoint::set_field(int field, const void *srcv) {
+    const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+    const size_t row = (size_t)lat_->nx * rs_;
+    char *base = (char *)adj_[cur_] + (size_t)field * lat_->plane_elems * rs_;
+    if (dev) ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
+    for (int z = 0; z < lat_->nz; z++) {
+        char *d = base + ((size_t)(z + lat_->gz) * lat_->NY + lat_->gy) * row;
+        const char *s = (const char *)srcv + (size_t)z * lat_->ny * row;
+        if (dev) ADJ_CUDA(cudaMemcpy2D(d, row, s, row, row, lat_->ny, cudaMemcpyHostToDevice));
+        else for (int y = 0; y < lat_->ny; y++) memcpy(d + y * row, s + y * row, row);
+    }
+}
+double Adjoint::dot_field(int field, const void *dir) const {
+    const size_t n = (size_t)lat_->nx * lat_->ny * lat_->nz;
+    std::vector<char> tmp(n * rs_);
+    get_field(field, tmp.data());
+    double s = 0;
+    if (rs_ == 8) { const double *a = (const double *)tmp.data(), *b = (const double *)dir; for (size_t i = 0; i < n; i++) s += a[i] * b[i]; }
+    else { const float *a = (const float *)tmp.data(), *b = (const float *)dir; for (size_t i = 0; i < n; i++) s += (double)a[i] * b[i]; }
+    return s;
+}
+
+}  // namespace tclb

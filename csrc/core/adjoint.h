@@ -1,0 +1,55 @@
+// Discrete adjoint driver: reverse sweep over a recorded primal run, or fixed-point iteration at a converged state.
+//
+// Role of the reference's adjoint machinery (Lattice::IterateTillAdjoint / snapshots "tape" levels,
+// src/Lattice.cu.Rt:536-700; handlers acUSAdjoint / acSAdjoint), built differently: the stage adjoint comes from the
+// dual-number build of the model library (libtclb_<model>_<prec>_ad.so, tclb_b200/gen/adjoint.cu.in), the tape is a
+// list of whole input snapshots (device memory first, host memory beyond TCLB_TAPE_DEVICE_BYTES), and the halo
+// transpose is a ghost fold.  This version covers actions made of ONE stage on ONE subdomain.
+#pragma once
+#include <string>
+#include <vector>
+#include "lattice.h"
+
+namespace tclb {
+
+class Adjoint {
+  public:
+    explicit Adjoint(Domain *dom);
+    ~Adjoint();
+    Adjoint(const Adjoint &) = delete;
+    // ---- unsteady ----
+    void record(int n);          // n primal iterations with the input of each kept on the tape; Objective accumulated
+    void reverse();              // sweep the tape backwards; afterwards adjoint() is dObjective/d(state at the start)
+    void drop_tape();
+    size_t tape_length() const { return tape_.size(); }
+    // ---- steady ----
+    void steady(int n);          // n adjoint iterations around the current state (input of the next primal iteration)
+    // ---- access ----
+    double objective = 0.0;      // sum over the recorded iterations of the Objective global
+    void zero();
+    void get_field(int field, void *dst_real) const;    // interior [nz][ny][nx] of the adjoint of `field`, in real_t
+    void set_field(int field, const void *src_real);    // seed (e.g. d(cost)/d(final state))
+    double dot_field(int field, const void *dir_real) const;   // sum adjoint * dir over the interior
+    int real_size() const { return rs_; }
+  private:
+    typedef int (*stage_fn)(int, const tclb_launch_t *, const void *, void *);
+    typedef const char *(*err_fn)(void);
+    struct Frame { void *data; bool on_device; int iter; };
+    Domain *dom_;
+    Lattice *lat_;
+    void *lib_ = nullptr;
+    stage_fn fn_ = nullptr;
+    err_fn err_ = nullptr;
+    int rs_ = 8, action_ = -1, stage_ = -1;
+    void *adj_[2] = {nullptr, nullptr};
+    int cur_ = 0;
+    size_t bytes_ = 0;           // one adjoint buffer = n_fields * plane_elems * real_size
+    std::vector<Frame> tape_;
+    size_t dev_tape_bytes_ = 0, dev_tape_cap_ = 0;
+    void step(const void *primal_in, int iter);   // adj_[cur^1] = J^T adj_[cur] + dObj; then swap
+    void *alloc(size_t bytes, bool device) const;
+    void release(void *p, bool device) const;
+    void fill_zero(void *p) const;
+};
+
+}  // namespace tclb

@@ -2,6 +2,7 @@
 #include "tclb_b200.h"
 #include "common.h"
 #include "lattice.h"
+#include "adjoint.h"
 #include <cmath>
 #include <cstring>
 #include <cuda_runtime.h>
@@ -142,6 +143,8 @@ int tclb_domain_set_field(tclb_domain_h *h, int rank, const char *f, const void 
     int i = h->d->model->find_field(f);
     if (i < 0) fail("unknown field %s", f);
     rank_lat(h, rank)->copy_field_in(i, src);
+    // keep the ghost layers consistent with the new interior (all subdomains in this process: plain copies)
+    if ((int)h->d->local.size() == h->d->dec.nranks) h->d->copy_exchange(rank_lat(h, rank)->cur);
     GUARD_END_INT
 }
 int tclb_domain_get_quantity(tclb_domain_h *h, int rank, const char *q, const int *b6, void *dst, double scale) {
@@ -312,3 +315,31 @@ int tclb_solver_zone_id(tclb_solver_h *h, const char *name) {
 tclb_domain_h *tclb_solver_domain(tclb_solver_h *h) { return h->dom.d ? &h->dom : nullptr; }
 int tclb_solver_iter(tclb_solver_h *h) { return h->s->iter; }
 const char *tclb_solver_outpath(tclb_solver_h *h) { return h->s->outpath.c_str(); }
+
+// ---- adjoint (csrc/core/adjoint.h) ----
+struct tclb_adjoint_h { Adjoint *a; };
+tclb_adjoint_h *tclb_adjoint_create(tclb_domain_h *h) {
+    GUARD_BEGIN
+    return new tclb_adjoint_h{new Adjoint(h->d)};
+    GUARD_END_PTR
+}
+void tclb_adjoint_destroy(tclb_adjoint_h *a) { if (a) { delete a->a; delete a; } }
+int tclb_adjoint_record(tclb_adjoint_h *a, int n) { GUARD_BEGIN a->a->record(n); GUARD_END_INT }
+int tclb_adjoint_reverse(tclb_adjoint_h *a) { GUARD_BEGIN a->a->reverse(); GUARD_END_INT }
+int tclb_adjoint_steady(tclb_adjoint_h *a, int n) { GUARD_BEGIN a->a->steady(n); GUARD_END_INT }
+int tclb_adjoint_zero(tclb_adjoint_h *a) { GUARD_BEGIN a->a->zero(); a->a->objective = 0; GUARD_END_INT }
+double tclb_adjoint_objective(tclb_adjoint_h *a) { return a->a->objective; }
+int tclb_adjoint_get_field(tclb_adjoint_h *a, tclb_domain_h *h, const char *f, void *dst) {
+    GUARD_BEGIN
+    int i = h->d->model->find_field(f);
+    if (i < 0) fail("unknown field %s", f);
+    a->a->get_field(i, dst);
+    GUARD_END_INT
+}
+int tclb_adjoint_set_field(tclb_adjoint_h *a, tclb_domain_h *h, const char *f, const void *src) {
+    GUARD_BEGIN
+    int i = h->d->model->find_field(f);
+    if (i < 0) fail("unknown field %s", f);
+    a->a->set_field(i, src);
+    GUARD_END_INT
+}

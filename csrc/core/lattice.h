@@ -138,6 +138,7 @@ class Lattice {
     bool has_nan(int q, const Box &local_box);
 
   private:
+    friend class Adjoint;          // adjoint.h: launches the adjoint stage with this lattice's launch parameters
     Arena arena_;
     void *snap_[2];
     void *flags_;

@@ -1,0 +1,58 @@
+// Helpers of the adjoint sweep that do not depend on the model (float and double lattices).
+//
+// tclb_adjoint_fold_ghosts: the adjoint stage scatters into the cells its inputs were pulled from, which includes the
+// y/z ghost layers; a ghost cell is an image of an interior cell of the periodic neighbour (here: the same subdomain,
+// wrapped), so its value is added to that cell and cleared.  The primal halo is a copy owner -> ghost; this is its
+// transpose.  (Reference: the adjoint border kernels + reversed MPI exchange, src/Lattice.cu.Rt:589-640.)
+#include <cuda_runtime.h>
+#include <cstdio>
+
+namespace {
+template <class T>
+__global__ void k_fold_ghosts(T *adj, int nfields, int nx, int ny, int nz, int gy, int gz) {
+    const int NY = ny + 2 * gy, NZ = nz + 2 * gz;
+    const long long plane = (long long)nx * NY * NZ;
+    const long long n = (long long)nfields * plane;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i % plane;
+        const int x = (int)(r % nx);
+        const int Y = (int)((r / nx) % NY), Z = (int)(r / ((long long)nx * NY));
+        const int y = Y - gy, z = Z - gz;
+        if (y >= 0 && y < ny && z >= 0 && z < nz) continue;
+        const T v = adj[i];
+        if (v == (T)0) continue;
+        const int yy = ((y % ny) + ny) % ny, zz = ((z % nz) + nz) % nz;
+        atomicAdd(&adj[(i - r) + ((long long)(zz + gz) * NY + (yy + gy)) * nx + x], v);
+        adj[i] = (T)0;
+    }
+}
+template <class T>
+void fold_host(T *adj, int nfields, int nx, int ny, int nz, int gy, int gz) {
+    const int NY = ny + 2 * gy, NZ = nz + 2 * gz;
+    const long long plane = (long long)nx * NY * NZ;
+    for (int f = 0; f < nfields; f++)
+        for (int Z = 0; Z < NZ; Z++)
+            for (int Y = 0; Y < NY; Y++) {
+                const int y = Y - gy, z = Z - gz;
+                if (y >= 0 && y < ny && z >= 0 && z < nz) continue;
+                const int yy = ((y % ny) + ny) % ny, zz = ((z % nz) + nz) % nz;
+                T *src = adj + f * plane + ((long long)Z * NY + Y) * nx;
+                T *dst = adj + f * plane + ((long long)(zz + gz) * NY + (yy + gy)) * nx;
+                for (int x = 0; x < nx; x++) { dst[x] += src[x]; src[x] = (T)0; }
+            }
+}
+}  // namespace
+
+extern "C" int tclb_adjoint_fold_ghosts(void *adj, int real_size, int on_device, int nfields, int nx, int ny, int nz, int gy, int gz,
+                                        void *stream) {
+    if (gy == 0 && gz == 0) return 0;
+    if (!on_device) {
+        if (real_size == 8) fold_host((double *)adj, nfields, nx, ny, nz, gy, gz);
+        else fold_host((float *)adj, nfields, nx, ny, nz, gy, gz);
+        return 0;
+    }
+    const int tb = 256, nb = 148 * 8;
+    if (real_size == 8) k_fold_ghosts<double><<<nb, tb, 0, (cudaStream_t)stream>>>((double *)adj, nfields, nx, ny, nz, gy, gz);
+    else k_fold_ghosts<float><<<nb, tb, 0, (cudaStream_t)stream>>>((float *)adj, nfields, nx, ny, nz, gy, gz);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}

@@ -102,6 +102,25 @@ const char *tclb_scan_last_error(void);
 int tclb_scan_array_static(const void *dev_ptr, long long n, int real_size, void *stream, double *result3_dev,
                            char *err, int err_cap);
 
+/* ---- discrete adjoint (csrc/core/adjoint.h; reference: Tapenade adjoint + acUSAdjoint/acSAdjoint handlers) ----
+ * Needs the adjoint companion of the model library (libtclb_<model>_<precision>_ad.so, built by
+ * tclb_b200.build.build_adjoint_lib).  One subdomain, single-stage Iteration action.
+ *   record(n):  n primal iterations, inputs kept on a tape, Objective summed into tclb_adjoint_objective
+ *   reverse():  backward sweep over the tape; afterwards get_field(f) = dObjective / d(field f at the start);
+ *               for a parameter field (constant in time) that is the gradient with respect to the parameter
+ *   steady(n):  n adjoint iterations around the current state
+ *   set_field:  seed the adjoint (e.g. the derivative of a terminal cost) before reverse()/steady() */
+typedef struct tclb_adjoint_h tclb_adjoint_h;
+tclb_adjoint_h *tclb_adjoint_create(tclb_domain_h *);
+void tclb_adjoint_destroy(tclb_adjoint_h *);
+int tclb_adjoint_record(tclb_adjoint_h *, int n);
+int tclb_adjoint_reverse(tclb_adjoint_h *);
+int tclb_adjoint_steady(tclb_adjoint_h *, int n);
+int tclb_adjoint_zero(tclb_adjoint_h *);
+double tclb_adjoint_objective(tclb_adjoint_h *);
+int tclb_adjoint_get_field(tclb_adjoint_h *, tclb_domain_h *, const char *field, void *dst_real);
+int tclb_adjoint_set_field(tclb_adjoint_h *, tclb_domain_h *, const char *field, const void *src_real);
+
 /* ---- units (reference src/unit.{h,cpp}) ---- */
 typedef struct tclb_units_h tclb_units_h;
 tclb_units_h *tclb_units_create(void);

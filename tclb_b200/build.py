@@ -180,6 +180,31 @@ def build_model_lib(variant: str, precision: str = "float", force: bool = False,
     return target
 
 
+def build_adjoint_lib(variant: str, precision: str = "double", dirs: int = 4, force: bool = False) -> Path:
+    """The adjoint companion of a model library: the same generated source compiled with -DTCLB_AD (node code in dual
+    numbers, csrc/kernels/tclb_dual.h), exporting ``tclb_model_adjoint_stage``.  The runtime loads
+    ``libtclb_<variant>_<precision>_ad.so`` next to the primal library when an adjoint is asked for.  `variant` is a
+    native model name or the name of an already generated source (``ref_<model>`` after build_from_dir)."""
+    if precision not in ("float", "double"):
+        raise ValueError("adjoint libraries use plain float/double storage")
+    LIBDIR.mkdir(parents=True, exist_ok=True)
+    src = GENDIR / f"{variant}.cu"
+    if not (variant.startswith("ref_") and src.exists()):
+        src = generate_model(variant)
+    target = LIBDIR / f"libtclb_{variant}_{precision}_ad.so"
+    hdrs = [ROOT / "include" / "tclb_model_abi.h", ROOT / "csrc" / "kernels" / "tclb_node_rt.h", ROOT / "csrc" / "kernels" / "tclb_dual.h"]
+    extra = ["-DTCLB_AD", f"-DTCLB_AD_DIRS={int(dirs)}"]
+    digest = _hash([src] + hdrs, precision + " ".join(NVCC_FLAGS + ARCH_FLAGS + extra))
+    if not force and _stamp_ok(target, digest):
+        return target
+    cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + extra + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
+    cmd += precision_flags(precision)
+    cmd += ["-o", str(target), str(src), "-lgomp"]
+    _run(cmd, ROOT / "build" / "logs" / f"{variant}_{precision}_ad.ptxas.log")
+    _stamp(target, digest)
+    return target
+
+
 def build_custom(modeldef, libname: str, precision: str = "double", extra_flags=()) -> Path:
     """Compile a ModelDef object under an explicit library name (tests, experiments, user models)."""
     from .gen.emit import emit_model_source

@@ -121,7 +121,8 @@ _PARTICLES = r"""
 #define RFI_DATA_MOMENT 13
 #define RFI_DATA_SIZE 16
 #define PART_MAR ((real_t)@PART_MAR@)
-TCLB_HD void particle_atomic_add(real_t *p, real_t v) {
+TCLB_HD void particle_atomic_add(base_t *p, real_t v_) {
+    const base_t v = tclb_value(v_);
 #ifdef __CUDA_ARCH__
     atomicAdd(p, v);
 #else
@@ -135,8 +136,8 @@ struct Particle {
     TCLB_HD bool in() const { return dist < rad; }
 };
 struct ParticleI : Particle {
-    real_t *row;
-    TCLB_HD ParticleI(real_t *row_, real_t x, real_t y, real_t z) : row(row_) {
+    base_t *row;
+    TCLB_HD ParticleI(base_t *row_, real_t x, real_t y, real_t z) : row(row_) {
         rad = row[RFI_DATA_R];
         diff.x = x - row[RFI_DATA_POS + 0]; diff.y = y - row[RFI_DATA_POS + 1]; diff.z = z - row[RFI_DATA_POS + 2];
         dist = sqrt(diff.x * diff.x + diff.y * diff.y + diff.z * diff.z);
@@ -149,7 +150,7 @@ struct ParticleI : Particle {
 struct ParticleS : ParticleI {
     vector_t force, moment;
     bool touched;
-    TCLB_HD ParticleS(real_t *row_, real_t x, real_t y, real_t z) : ParticleI(row_, x, y, z), touched(false) {
+    TCLB_HD ParticleS(base_t *row_, real_t x, real_t y, real_t z) : ParticleI(row_, x, y, z), touched(false) {
         force.x = force.y = force.z = 0;
         moment.x = moment.y = moment.z = 0;
     }
@@ -170,11 +171,11 @@ struct ParticleS : ParticleI {
 };
 template <class P>
 struct ParticleRange {
-    real_t *data;
+    base_t *data;
     int n;
     real_t x, y, z;
     TCLB_HD bool near(int i) const {
-        const real_t *row = data + (size_t)i * RFI_DATA_SIZE;
+        const base_t *row = data + (size_t)i * RFI_DATA_SIZE;
         const real_t rr = row[RFI_DATA_R] + PART_MAR;
         return fabs(x - row[RFI_DATA_POS + 0]) <= rr && fabs(y - row[RFI_DATA_POS + 1]) <= rr && fabs(z - row[RFI_DATA_POS + 2]) <= rr;
     }
@@ -208,8 +209,14 @@ def emit_model_source(m: ModelDef, libname: str) -> str:
     A = L.append
     A(f"// GENERATED by tclb_b200.gen.emit -- model {m.name} ({libname}); do not edit.")
     A('#include "tclb_node_rt.h"')
-    A("#ifdef TCLB_DOUBLE\ntypedef double real_t;\n#define TCLB_REAL_NAME \"double\"\n#else\ntypedef float real_t;\n#define TCLB_REAL_NAME \"float\"\n#endif")
+    A("#ifdef TCLB_DOUBLE\ntypedef double base_t;\n#define TCLB_REAL_NAME \"double\"\n#else\ntypedef float base_t;\n#define TCLB_REAL_NAME \"float\"\n#endif")
+    # adjoint build (-DTCLB_AD, csrc/kernels/tclb_dual.h): the node code computes in dual numbers, memory stays base_t
+    A("#ifdef TCLB_AD\n#include \"tclb_dual.h\"\ntypedef Dual<base_t, TCLB_AD_DIRS> real_t;\n#else\ntypedef base_t real_t;\n#endif")
     A("typedef tclb_vec3<real_t> vector_t;")
+    # Color() of a model assigns real_t expressions to a float2; the adjoint build never calls it, so there the
+    # members just swallow what they are given
+    A("#ifdef TCLB_AD\nstruct tclb_ad_sink { template <class U> TCLB_HD tclb_ad_sink &operator=(const U &) { return *this; } };\n"
+      "struct tclb_ad_float2 { tclb_ad_sink x, y; };\n#define float2 tclb_ad_float2\n#endif")
     # storage type of the lattice (reference ./configure --with-storage=half|half-shift|float|float-shift|double,
     # src/LatticeAccess.inc.cpp.Rt:14-35): what lives in HBM may be narrower than what the node code computes in, and a
     # per-field constant (AddDensity(shift=)) may be subtracted before storing so that small deviations keep their bits
@@ -225,7 +232,7 @@ typedef float storage_t;
 #define storage_to_real(v__) ((real_t)(v__))
 #define real_to_storage(v__) ((float)(v__))
 #else
-typedef real_t storage_t;
+typedef base_t storage_t;
 #define TCLB_STORAGE_NAME TCLB_REAL_NAME
 #define storage_to_real(v__) (v__)
 #define real_to_storage(v__) (v__)
@@ -288,11 +295,11 @@ struct KArgs {
     double *globals;
     double *gl_ring[TCLB_MAX_RANKS];
     unsigned *gl_counter;
-    real_t *gl_partial;
+    base_t *gl_partial;
     long long gl_partial_stride;
     unsigned gl_epoch;
     int gl_publish, gl_rank, gl_nranks, n_blocks;
-    const real_t *zone;
+    const base_t *zone;
     int zone_len, zone_index, zone_stride;
     int iter, reset_iter;
     storage_t *halo[9];
@@ -308,7 +315,7 @@ struct KArgs {
     real_t qscale;
     const tclb_st_mode_t *st;
     int st_n;
-    real_t *particles;           // [n_particles][16]: r, pos, vel, angular velocity, force, moment (RFI layout)
+    base_t *particles;           // [n_particles][16]: r, pos, vel, angular velocity, force, moment (RFI layout)
     int n_particles;
     // launches captured in a CUDA graph take iteration and halo epoch from device memory (dyn[0], dyn[1] = values at
     // the start of the graph) plus a constant offset, so one instantiated graph can be replayed; NULL otherwise
@@ -451,14 +458,15 @@ struct Node {
         }
         return v;
     }
-    // Globals: SUM globals also add the zone's <Global>InObj weight to Objective, exactly as the
-    // reference does (src/cuda.cu.Rt:113-119 adds the weight itself, not weight*x).
+    // Globals: SUM globals also add (zone's <Global>InObj weight) * x to Objective.  The reference's line
+    // (src/cuda.cu.Rt:113-119) adds the weight WITHOUT the factor x, which makes Objective independent of the
+    // flow; the product is what its optimisation handlers document and what the adjoint here differentiates.
     // GMODE bits: 1 = accumulate every Global, 2 = add the InObj weights to Objective.  The launcher picks the
     // variant without bit 2 when every weight is zero (the usual case), so the hot kernel carries no weight loads.
     template <int I> TCLB_HD void AddToGlobal(real_t x) {
         if (GMODE & 1) gacc_[I * GSTRIDE] += x;
         if ((GMODE & 2) && I < SUM_GLOBALS && I != GLOBALS_Objective)
-            gacc_[((GMODE & 1) ? GLOBALS_Objective : 0) * GSTRIDE] += zone_setting(I + IN_OBJ_OFFSET);
+            gacc_[((GMODE & 1) ? GLOBALS_Objective : 0) * GSTRIDE] += zone_setting(I + IN_OBJ_OFFSET) * x;
     }
     template <int I> TCLB_HD void MaxToGlobal(real_t x) {
         if (GMODE & 1) gacc_[I * GSTRIDE] = tclbrt::tmax(gacc_[I * GSTRIDE], x);
@@ -557,6 +565,53 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     A("}")
 
     A(_SCAFFOLD)
+
+    # ---- adjoint build: seeds, collection and scatter per stage (see adjoint.cu.in) ----
+    A("#ifdef TCLB_AD")
+    A("TCLB_HD void ad_add(base_t *p, base_t v);")
+    loaded = [[(di, d) for di, d in enumerate(m.densities) if d.load.get(s.name)] for s in m.stages]
+    A("TCLB_HD int ad_inputs_of_stage(int s) {\n    switch (s) {")
+    for si in range(len(m.stages)):
+        A(f"    case {si}: return {len(loaded[si])};")
+    A("    default: return 0;\n    }\n}")
+    for si, s in enumerate(m.stages):
+        A(f"template <int GMODE> TCLB_HD void ad_seed_stage_{si}(Node<GMODE> &n, int c) {{")
+        for k, (di, d) in enumerate(loaded[si]):
+            A(f"    if (c == {k} / TCLB_AD_DIRS) n.{d.name}.d[{k} % TCLB_AD_DIRS] = 1;")
+        A("}")
+        A(f"template <int GMODE> TCLB_HD real_t ad_collect_stage_{si}(Node<GMODE> &n, const KArgs &a, const base_t *adj_out) {{")
+        A("    real_t g = 0;")
+        for f in m.fields:
+            if f.save.get(s.name):
+                A(f"    g += n.{f.name} * adj_out[{fidx[f.name]} * a.fstride + n.n_idx];")
+        A("    return g;\n}")
+        A(f"TCLB_HD void ad_scatter_stage_{si}(const KArgs &a, base_t *adj_in, int x, int i0, int im, int ip, int c, const real_t &g) {{")
+        for k, (di, d) in enumerate(loaded[si]):
+            A(f"    if (c == {k} / TCLB_AD_DIRS) ad_add(adj_in + (a.ldp[{di}] - a.in) + ({_xidx(d.dx)}), g.d[{k} % TCLB_AD_DIRS]);")
+        A("}")
+    A("template <int S, int GMODE> TCLB_HD void ad_seed_stage(Node<GMODE> &n, int c) {")
+    for si in range(len(m.stages)):
+        A(f"    if (S == {si}) ad_seed_stage_{si}(n, c);")
+    A("}")
+    A("template <int S, int GMODE> TCLB_HD real_t ad_collect_stage(Node<GMODE> &n, const KArgs &a, const base_t *adj_out) {")
+    for si in range(len(m.stages)):
+        A(f"    if (S == {si}) return ad_collect_stage_{si}(n, a, adj_out);")
+    A("    return real_t(0);\n}")
+    A("template <int S> TCLB_HD void ad_scatter_stage(const KArgs &a, base_t *adj_in, int x, int i0, int im, int ip, int c, const real_t &g) {")
+    for si in range(len(m.stages)):
+        A(f"    if (S == {si}) ad_scatter_stage_{si}(a, adj_in, x, i0, im, ip, c, g);")
+    A("}")
+    A(_AD_SCAFFOLD)
+    A("}  // namespace")
+    A('extern "C" int tclb_model_adjoint_stage(int stage, const tclb_launch_t *L, const void *adj_out, void *adj_in) {')
+    A("    KArgs a; int bx, by; fill_args(a, L, bx, by);")
+    A("    switch (stage) {")
+    for si in range(len(m.stages)):
+        A(f"    case {si}: return run_adjoint_stage<{si}>(a, L, (const base_t *)adj_out, (base_t *)adj_in);")
+    A('    default: set_error("bad stage"); return -1;\n    }\n}')
+    A('extern "C" const char *tclb_model_adjoint_error(void) { return g_error; }')
+    A(f'extern "C" int tclb_model_adjoint_info(int *real_size, int *dirs, int *n_fields) {{ *real_size = (int)sizeof(base_t); *dirs = TCLB_AD_DIRS; *n_fields = N_FIELDS; return TCLB_ABI_VERSION; }}')
+    A("#else  // !TCLB_AD")
 
     # ---- dispatch tables ----
     A("int run_stage_impl(int stage, const tclb_launch_t *L) {")
@@ -666,8 +721,10 @@ const tclb_model_t t_model = {{
 }};
 }}  // namespace
 extern "C" const tclb_model_t *tclb_get_model(void) {{ return &t_model; }}
+#endif  // !TCLB_AD
 """)
     return "\n".join(L) + "\n"
 
 
 _SCAFFOLD = (Path(__file__).with_name("scaffold.cu.in")).read_text()
+_AD_SCAFFOLD = (Path(__file__).with_name("adjoint.cu.in")).read_text()

@@ -93,7 +93,7 @@ def integer_orthogonalise(M: np.ndarray) -> np.ndarray:
 
 
 def mrt_eq(U, rho="rho", J=("Jx", "Jy", "Jz"), sigma2=1.0 / 3.0, order: int = 2,
-           orthogonal: bool = True, mat: Optional[np.ndarray] = None) -> Equilibrium:
+           orthogonal: bool = True, mat: Optional[np.ndarray] = None, correction=None) -> Equilibrium:
     """Equilibrium moments: rho * prod_k {1, J_k/rho, J_k^2/rho^2 + sigma2}, truncated at
     `order` in J, expressed either in the raw monomial basis, an integer-orthogonalised one
     or a user matrix `mat`."""
@@ -120,6 +120,14 @@ def mrt_eq(U, rho="rho", J=("Jx", "Jy", "Jz"), sigma2=1.0 / 3.0, order: int = 2,
         # momentum may be given as a product such as d*u[0], whose density factor must not count
         count = [sy for sy in h.symbols() if sy not in rho_syms]
         H.append(h.truncate(count, order))
+    if correction is not None:
+        # added to the raw moments of order > 3, before any change of basis (reference src/lib/feq.R:59-63)
+        sel = [j for j in range(U.shape[0]) if B.order[j] > 3]
+        corr = list(correction)
+        if len(sel) != len(corr):
+            raise ValueError("Correction of wrong length in MRT_eq")
+        for j, c in zip(sel, corr):
+            H[j] = H[j] + c
     Req = PVec(H)
     Mat = B.mat
     ordr = B.order.copy()

@@ -412,6 +412,9 @@ def install(I):
                     continue
                 d = x if d is None or not d.cols else d.rbind(x)
             return d
+        if any(isinstance(x, (Poly, PVec)) for x in items):
+            # symbolic scalars stacked into a column (only the one-column case occurs in the models)
+            return _c(I, items, OrderedDict())
         rows = [vec(x) if vec(x).ndim == 2 else vec(x).reshape(1, -1) for x in items]
         return np.vstack(rows)
 
@@ -630,7 +633,13 @@ def install_poly(I):
                 out.append(Poly.sym("".join(to_str(t) for t in toks)))
         return PVec(out)
     G.set("PV", _pv)
-    G.set("V", lambda I, a, k: a[0] if isinstance(a[0], PVec) else PVec([a[0]]) if isinstance(a[0], Poly) else PVec([float(v) for v in vec(a[0]).tolist()]))
+    def _V(I, a, k):
+        """gvector V(...): every argument, flattened, as one symbolic vector"""
+        out = []
+        for x in a:
+            out += list(x) if isinstance(x, PVec) else [x] if isinstance(x, Poly) else [Poly.const(float(v)) for v in vec(x).ravel(order="F").tolist()]
+        return PVec(out)
+    G.set("V", _V)
 
     def _toc(I, a, k):
         x = a[0]

@@ -159,21 +159,25 @@ def all_option_names(opt: str) -> List[str]:
 
 
 def load_dynamics_r(model_dir: str, name: Optional[str] = None, options: Optional[Dict[str, bool]] = None,
-                    reference_src: Optional[str] = None, finalize: bool = True):
-    """Evaluate <model_dir>/Dynamics.R and return (ModelDef, Interp)."""
+                    reference_src: Optional[str] = None, finalize: bool = True, primal_only: bool = True):
+    """Evaluate <model_dir>/Dynamics.R and return (ModelDef, Interp).
+
+    `primal_only` (default): a model whose conf.mk says ADJOINT=1 is built as its primal part (the reference's
+    `#ifdef ADJOINT` sections left out); `ModelDef.adjoint_requested` keeps what conf.mk asked for."""
     name = name or os.path.basename(os.path.normpath(model_dir))
     conf = parse_conf_mk(os.path.join(model_dir, "conf.mk"))
     opts = {o: False for o in all_option_names(conf.get("OPT", ""))}
     opts["autosym"] = 0
     opts.update(options or {})
-    m = ModelDef(name, opts, adjoint=conf["ADJOINT"])
+    m = ModelDef(name, opts, adjoint=0 if primal_only else conf["ADJOINT"])
+    m.adjoint_requested = conf["ADJOINT"]
     I = Interp(include_dirs=[model_dir] + ([reference_src, os.path.join(reference_src, "lib")] if reference_src else []))
     env = _ModelEnv(m)
     env.vars.update(I.globals.vars)
     I.globals = env
     env.set("Options", RList.make([vec(bool(v)) if isinstance(v, bool) else vec(v) for v in opts.values()], list(opts.keys())))
     env.set("MODEL", vec(name))
-    env.set("ADJOINT", vec(conf["ADJOINT"]))
+    env.set("ADJOINT", vec(m.adjoint))
     env.set("include.dir", vec(model_dir))
 
     import inspect

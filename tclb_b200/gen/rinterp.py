@@ -743,7 +743,7 @@ class Interp:
                                 d.cols[kk] = [NA] * d.nrow()
                     else:
                         keys = [list(d.cols)[c] for c in self._pos_index(idxs[1], d.ncol(), list(d.cols))]
-                    v = vec(val).tolist()
+                    v = [x for col in val.cols.values() for x in col] if isinstance(val, DataFrame) else vec(val).ravel(order="F").tolist()
                     t = 0
                     for kk in keys:
                         for r in rows:

@@ -156,22 +156,17 @@ def install_feq(I, env):
         order = int(scalar(g["order"])) if "order" in g else 2
         orth = truthy(g["ortogonal"]) if "ortogonal" in g else True
         mat = _mat(g["mat"]) if "mat" in g and g["mat"] is not NULL else known_matrix(U)
-        eq = lbmlib.mrt_eq(U, rho=rho, J=J, sigma2=sigma2, order=order, orthogonal=orth, mat=mat)
+        try:
+            eq = lbmlib.mrt_eq(U, rho=rho, J=J, sigma2=sigma2, order=order, orthogonal=orth, mat=mat,
+                               correction=_pvec(g["correction"]) if "correction" in g else None)
+        except ValueError as e:
+            raise RError(str(e))
         extra = {}
         if mat is None and not orth:
             B = lbmlib.poly_moment_matrix(U)
             extra["p"] = B.p.astype(float)
             p = np.where(U < 0, 2, U)
             extra["canonical"] = (np.argsort(p.sum(axis=1), kind="stable") + 1).astype(float)
-        if "correction" in g:
-            corr = _pvec(g["correction"])
-            sel = np.nonzero(np.asarray(eq.order) > 3)[0]
-            if len(sel) != len(corr):
-                raise RError("Correction of wrong length in MRT_eq")
-            Req = eq.Req.copy()
-            for i, c in zip(sel, corr):
-                Req[int(i)] = Req[int(i)] + c
-            eq = lbmlib.Equilibrium(U=eq.U, Req=Req, mat=eq.mat, order=eq.order, feq=Req @ np.linalg.inv(eq.mat), rho=eq.rho, J=eq.J)
         r = _eq_to_rlist(eq, None)
         for kk, v in extra.items():
             r[kk] = v

@@ -34,6 +34,9 @@ def template_to_program(text: str, texts: List[str]) -> str:
             out.append(f".rt_include({body.strip()!r})" if not body.strip().startswith(("'", '"')) else f".rt_include({body.strip()})")
         elif kind.startswith("%"):
             out.append(f".rt_fmt({kind!r}, {body.strip()})")
+        elif kind == "python":
+            texts.append(body)
+            out.append(f".rt_python({len(texts) - 1})")
         else:
             raise RError(f"template tag <?{kind} is not supported")
         pos = m.end()
@@ -42,6 +45,54 @@ def template_to_program(text: str, texts: List[str]) -> str:
         texts.append(lit)
         out.append(f".rt_text({len(texts) - 1})")
     return "\n".join(out) + "\n"
+
+
+_PY_TABLES = ("Density", "DensityAll", "DensityAD", "Fields", "Settings", "ZoneSettings", "Globals", "Quantities", "NodeTypes",
+              "Stages", "Actions")
+_PY2_PRINT = re.compile(r"^(\s*)print[ \t]+(?!\()(.+?)[ \t]*$", re.M)
+
+
+def run_python_chunk(I: Interp, env: Env, body: str) -> str:
+    """``<?python ... ?>``: Python embedded in a model template.  Running it means executing code that ships with the
+    model directory, so it is OFF unless the user opts in with ``TCLB_ALLOW_PYTHON_CHUNKS=1`` (only do that for model
+    files you trust).  When enabled, the chunks of one template share ONE namespace (a preamble chunk defines what later
+    chunks print), the model tables are visible as dicts of columns (what rPython hands over) and stdout goes into the
+    generated file.  The chunks in existing models were written for Python 2 + sympy (print statements, list-returning
+    zip/map, cStringIO), so those are provided."""
+    import builtins
+    import contextlib
+    import io
+    import sys
+    import textwrap
+    import types
+    from .rlang import DataFrame
+    if os.environ.get("TCLB_ALLOW_PYTHON_CHUNKS") != "1":
+        raise RError("template tag <?python is not supported unless TCLB_ALLOW_PYTHON_CHUNKS=1 (it executes Python code "
+                     "from the model directory)")
+    ns = getattr(I, "_py_namespace", None)
+    if ns is None:
+        if "cStringIO" not in sys.modules:
+            mod = types.ModuleType("cStringIO")
+            mod.StringIO = io.StringIO
+            sys.modules["cStringIO"] = mod
+        ns = {"__name__": "__tclb_template__", "zip": lambda *a: list(builtins.zip(*a)), "map": lambda *a: list(builtins.map(*a)),
+              "filter": lambda *a: list(builtins.filter(*a)), "xrange": range}
+        I._py_namespace = ns
+    for name in _PY_TABLES:
+        try:
+            v = env.get(name)
+        except RError:
+            continue
+        if isinstance(v, DataFrame):
+            ns[name] = {c: [x.item() if hasattr(x, "item") else x for x in col] for c, col in v.cols.items()}
+    code = _PY2_PRINT.sub(lambda m: f"{m.group(1)}print({m.group(2)})", textwrap.dedent(body.expandtabs(8)))
+    buf = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(buf):
+            exec(compile(code, "<?python chunk>", "exec"), ns)
+    except Exception as e:
+        raise RError(f"<?python chunk failed: {type(e).__name__}: {e}")
+    return buf.getvalue()
 
 
 def _read(path: str) -> str:
@@ -83,6 +134,11 @@ def render(I: Interp, env: Env, path: str, search: Optional[List[str]] = None) -
                 return NULL
         raise RError(f"template include not found: {name}")
 
+    def rt_python(I_, a, k):
+        I_.out.append(run_python_chunk(I_, env, texts[int(scalar(a[0]))]))
+        return NULL
+
+    env.set(".rt_python", rt_python)
     env.set(".rt_text", rt_text)
     env.set(".rt_fmt", rt_fmt)
     env.set(".rt_include", rt_include)

@@ -122,6 +122,9 @@ def core():
                                        C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_int), C.c_int]
     lib.tclb_domain_destroy.argtypes = [C.c_void_p]
     lib.tclb_domain_destroy.restype = None
+    lib.tclb_adjoint_create.restype = C.c_void_p
+    lib.tclb_adjoint_destroy.restype = None
+    lib.tclb_adjoint_objective.restype = C.c_double
     lib.tclb_domain_get_setting.restype = C.c_double
     lib.tclb_domain_snapshot_ptr.restype = C.c_void_p
     lib.tclb_domain_flags_ptr.restype = C.c_void_p
@@ -159,6 +162,15 @@ def core():
         "tclb_domain_import_peer": [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_int64), C.c_int, C.c_int],
         "tclb_domain_finalize_wiring": [C.c_void_p],
         "tclb_domain_set_hooks": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+        "tclb_adjoint_create": [C.c_void_p],
+        "tclb_adjoint_destroy": [C.c_void_p],
+        "tclb_adjoint_record": [C.c_void_p, C.c_int],
+        "tclb_adjoint_reverse": [C.c_void_p],
+        "tclb_adjoint_steady": [C.c_void_p, C.c_int],
+        "tclb_adjoint_zero": [C.c_void_p],
+        "tclb_adjoint_objective": [C.c_void_p],
+        "tclb_adjoint_get_field": [C.c_void_p, C.c_void_p, C.c_char_p, C.c_void_p],
+        "tclb_adjoint_set_field": [C.c_void_p, C.c_void_p, C.c_char_p, C.c_void_p],
     }.items():
         getattr(lib, fn).argtypes = args
     _core = lib
@@ -412,3 +424,61 @@ class Domain:
 
     def stream(self, rank: int) -> int:
         return int(self.lib.tclb_domain_stream(self.h, rank) or 0)
+
+
+class Adjoint:
+    """Discrete adjoint of a Domain (csrc/core/adjoint.h; the reference's <Adjoint> machinery).
+
+    Needs the adjoint companion library (``tclb_b200.build.build_adjoint_lib(model, precision)``).  Typical use::
+
+        adj = Adjoint(domain)
+        adj.record(100)            # 100 primal iterations on tape, adj.objective = sum of the Objective global
+        adj.reverse()              # backward sweep
+        g = adj.get_field("w")     # dObjective/dw for a parameter field w, or dObjective/d(initial f) for a density
+
+    One subdomain, Iteration actions of one stage, plain float/double storage."""
+
+    def __init__(self, domain: "Domain"):
+        self.domain = domain
+        self.lib = domain.lib
+        self.h = self.lib.tclb_adjoint_create(domain.h)
+        if not self.h:
+            raise NativeError(_s(self.lib.tclb_last_error()))
+
+    def close(self):
+        if self.h:
+            self.lib.tclb_adjoint_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def record(self, n: int):
+        _check(self.lib.tclb_adjoint_record(self.h, int(n)))
+
+    def reverse(self):
+        _check(self.lib.tclb_adjoint_reverse(self.h))
+
+    def steady(self, n: int):
+        _check(self.lib.tclb_adjoint_steady(self.h, int(n)))
+
+    def zero(self):
+        _check(self.lib.tclb_adjoint_zero(self.h))
+
+    @property
+    def objective(self) -> float:
+        return float(self.lib.tclb_adjoint_objective(self.h))
+
+    def get_field(self, name: str) -> np.ndarray:
+        nx, ny, nz = self.domain.shape
+        out = np.zeros((nz, ny, nx), dtype=self.domain.model.real_dtype)
+        _check(self.lib.tclb_adjoint_get_field(self.h, self.domain.h, name.encode(), out.ctypes.data))
+        return out
+
+    def set_field(self, name: str, values: np.ndarray):
+        nx, ny, nz = self.domain.shape
+        v = np.ascontiguousarray(values, dtype=self.domain.model.real_dtype).reshape(nz, ny, nx)
+        _check(self.lib.tclb_adjoint_set_field(self.h, self.domain.h, name.encode(), v.ctypes.data))

@@ -1,0 +1,90 @@
+"""Discrete adjoint (dual-number build of the model library + reverse sweep over a tape) against finite differences."""
+import numpy as np
+import pytest
+
+from tclb_b200 import build
+from tclb_b200.runtime import Adjoint, Domain, Model
+
+
+def _channel(m, shape, backend):
+    nx, ny, nz = shape
+    d = Domain(m, shape, backend, nranks=1)
+    fl = np.zeros((nz, ny, nx), dtype=np.uint32)
+    fl[:] = m.nodetypes["MRT"][0]
+    fl[:, 0, :] = m.nodetypes["Wall"][0]
+    fl[:, -1, :] = m.nodetypes["Wall"][0]
+    fl[:, 1:-1, 2] |= m.nodetypes["Inlet"][0]
+    fl[:, 1:-1, nx - 3] |= m.nodetypes["Outlet"][0]
+    d.set_flags(fl)
+    d.set_setting("Viscosity", 0.05)
+    d.set_setting("GravitationX", 1e-4)
+    d.set_setting("OutletFluxInObj", 1.0)
+    d.set_setting("PressureLossInObj", 0.5)
+    d.init()
+    d.iterate(20)
+    return d
+
+
+def _objective_sum(d, n):
+    tot = 0.0
+    for _ in range(n):
+        d.iterate(1, globals_every=True)
+        tot += d.globals()["Objective"]
+    return tot
+
+
+def _check_against_fd(backend, precision, eps, tol):
+    build.build_model_lib("d2q9", precision)
+    build.build_adjoint_lib("d2q9", precision)
+    m = Model("d2q9", precision)
+    shape = (24, 12, 1)
+    n = 6
+    d = _channel(m, shape, backend)
+    fields = list(m.fields)
+    base = {f: d.get_field(f).astype(np.float64) for f in fields}
+    adj = Adjoint(d)
+    adj.record(n)
+    J0 = adj.objective
+    adj.reverse()
+    grad = {f: adj.get_field(f).astype(np.float64) for f in fields}
+    assert J0 != 0.0 and any(np.abs(g).max() > 0 for g in grad.values())
+    rng = np.random.default_rng(3)
+    direction = {f: rng.standard_normal(base[f].shape) for f in fields}
+    predicted = sum(float((grad[f] * direction[f]).sum()) for f in fields)
+
+    def J(sign):
+        for f in fields:
+            d.set_field(f, base[f] + sign * eps * direction[f])
+        return _objective_sum(d, n)
+
+    fd = (J(+1) - J(-1)) / (2 * eps)
+    assert abs(fd - predicted) <= tol * max(abs(fd), abs(predicted)), (fd, predicted)
+    # the same run without the tape gives the same objective
+    for f in fields:
+        d.set_field(f, base[f])
+    assert abs(_objective_sum(d, n) - J0) <= 1e-6 * abs(J0) + (1e-12 if precision == "double" else 1e-4)
+    adj.close()
+    d.close()
+
+
+def test_adjoint_gradient_matches_finite_differences_cpu():
+    _check_against_fd("cpu", "double", 1e-6, 1e-6)
+
+
+def test_adjoint_needs_its_library(tmp_path):
+    build.build_model_lib("d2q9_SRT", "double")
+    m = Model("d2q9_SRT", "double")
+    d = Domain(m, (16, 8, 1), "cpu", nranks=1)
+    d.init()
+    import os
+    lib = build.LIBDIR / "libtclb_d2q9_SRT_double_ad.so"
+    if not lib.exists():
+        with pytest.raises(Exception, match="build_adjoint_lib"):
+            Adjoint(d)
+    d.close()
+
+
+@pytest.mark.gpu
+def test_adjoint_gradient_matches_finite_differences_gpu():
+    _check_against_fd("cuda", "double", 1e-6, 1e-6)
+    _check_against_fd("cuda", "float", 2e-3, 5e-2)

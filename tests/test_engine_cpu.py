@@ -118,8 +118,9 @@ def test_cumulant_central_equals_raw_formulation():
 
 
 def test_objective_weights_switch_on_with_zone_settings():
-    """<Global>InObj weights: Objective gets the zone's weight once per contribution (reference
-    src/cuda.cu.Rt:113-119); with every weight zero the kernels skip the terms and Objective stays 0."""
+    """<Global>InObj weights: Objective = sum over SUM Globals of (zone weight x contribution) (reference
+    src/cuda.cu.Rt:113-119, with the contribution kept: see DESIGN.md on the adjoint); with every weight zero the
+    kernels skip the terms and Objective stays 0."""
     from tclb_b200.runtime import Domain, Model
     m = Model("d3q27_cumulant", "double")
     shape = (32, 20, 16)
@@ -131,7 +132,8 @@ def test_objective_weights_switch_on_with_zone_settings():
     d.set_setting("MassInObj", 0.25)
     d.set_setting("FluxInObj", 2.0)
     d.iterate(1, globals_every=True)
-    assert abs(d.globals()["Objective"] - 2.25 * fluid) < 1e-9 * fluid
+    g = d.globals()
+    assert abs(g["Objective"] - (0.25 * g["Mass"] + 2.0 * g["Flux"])) < 1e-9 * fluid and g["Objective"] != 0.0
     d.set_setting("MassInObj", 0.0)
     d.set_setting("FluxInObj", 0.0)
     d.iterate(1, globals_every=True)

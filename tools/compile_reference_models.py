@@ -16,7 +16,7 @@ root = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
 only = sys.argv[2:]
 out = build.ROOT / "build" / "gen_try"
 out.mkdir(parents=True, exist_ok=True)
-OPTS = {"d2q9_scmp": {"Kupershtokh": True}, "d2q9_reaction_diffusion_system": {"SIR_SimpleLaplace": True}, "d3q27_PSM": {"NEBB": True}}
+OPTS = {"d2q9_scmp": {"Kupershtokh": True}, "d2q9_reaction_diffusion_system": {"AllenCahn": True}, "d3q27_PSM": {"NEBB": True}}
 jobs = []
 status = {}
 for d, _, files in sorted(os.walk(os.path.join(root, "models"))):
