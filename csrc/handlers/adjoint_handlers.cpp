@@ -1,0 +1,293 @@
+// Optimisation / adjoint elements of the case file.
+//
+// Reference: src/Handlers/acUSAdjoint.cpp, acSAdjoint.cpp (<Adjoint type=>), acOptSolve.cpp (<OptSolve>), acObjective.cpp
+// (<Objective>), acThresholdNow.cpp / acThreshold.cpp, acFDTest.cpp.  The adjoint itself is csrc/core/adjoint.h (dual
+// numbers instead of Tapenade), so these handlers drive a tape + reverse sweep instead of the reference's ITER_ADJOINT
+// iteration type; the design variables are the model's parameter fields (AddDensity(parameter=TRUE)) restricted to
+// nodes flagged DesignSpace when the model has that node type.
+#include "handler.h"
+#include "../core/adjoint.h"
+#include "../core/common.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <random>
+
+namespace tclb {
+namespace {
+
+Lattice *the_lattice(Solver *s) {
+    if (s->domain->local.size() != 1 || s->domain->dec.nranks != 1) fail("optimisation elements handle one subdomain in this version");
+    return s->domain->lat[s->domain->local[0]];
+}
+size_t n_nodes(Lattice *l) { return (size_t)l->nx * l->ny * l->nz; }
+void get_field_d(Solver *s, int f, std::vector<double> &v) {
+    Lattice *l = the_lattice(s);
+    const size_t n = n_nodes(l);
+    v.resize(n);
+    if (s->model->real_size() == 8) l->copy_field_out(f, v.data());
+    else { std::vector<float> t(n); l->copy_field_out(f, t.data()); for (size_t i = 0; i < n; i++) v[i] = t[i]; }
+}
+void set_field_d(Solver *s, int f, const std::vector<double> &v) {
+    Lattice *l = the_lattice(s);
+    if (s->model->real_size() == 8) l->copy_field_in(f, v.data());
+    else { std::vector<float> t(v.begin(), v.end()); l->copy_field_in(f, t.data()); }
+    s->domain->copy_exchange(l->cur);
+}
+void get_adj_d(Solver *s, int f, std::vector<double> &v) {
+    Lattice *l = the_lattice(s);
+    const size_t n = n_nodes(l);
+    v.resize(n);
+    if (s->model->real_size() == 8) s->need_adjoint()->get_field(f, v.data());
+    else { std::vector<float> t(n); s->need_adjoint()->get_field(f, t.data()); for (size_t i = 0; i < n; i++) v[i] = t[i]; }
+}
+void set_adj_d(Solver *s, int f, const std::vector<double> &v) {
+    if (s->model->real_size() == 8) s->need_adjoint()->set_field(f, v.data());
+    else { std::vector<float> t(v.begin(), v.end()); s->need_adjoint()->set_field(f, t.data()); }
+}
+// 1 where a design variable may change: nodes flagged DesignSpace, or everywhere when the model has no such type
+std::vector<char> design_mask(Solver *s) {
+    Lattice *l = the_lattice(s);
+    const size_t n = n_nodes(l);
+    std::vector<char> m(n, 1);
+    const tclb_nodetype_t *t = s->model->find_nodetype("DesignSpace");
+    if (!t) return m;
+    std::vector<uint32_t> fl(n);
+    Box b; b.x0 = b.y0 = b.z0 = 0; b.nx = l->nx; b.ny = l->ny; b.nz = l->nz;
+    l->get_flags(b, fl.data());
+    for (size_t i = 0; i < n; i++) m[i] = (fl[i] & t->mask) == t->value;
+    return m;
+}
+int objective_index(Solver *s) { return s->model->find_global("Objective"); }
+
+// <Adjoint type="unsteady"> children </Adjoint>: children run with every iteration on the tape, then the reverse sweep.
+// <Adjoint type="steady" Iterations="N"> children </Adjoint>: children run, then N adjoint iterations around the state
+// they left; parameter fields then hold the gradient contribution of ONE iteration (what a converged flow needs).
+class AcAdjoint : public GenericAction {
+  public:
+    int init() override {
+        GenericAction::init();
+        std::string type = node->attr("type");
+        if (type.empty()) type = node->has_attr("Iterations") ? "steady" : "unsteady";
+        Adjoint *A = solver->need_adjoint();
+        if (type == "unsteady") {
+            A->drop_tape(); A->zero(); A->objective = 0;
+            solver->recording = true;
+            int rc = execute_internal();
+            solver->recording = false;
+            if (rc) return -1;
+            const size_t n = A->tape_length();
+            if (n == 0) { logf(L_ERROR, "No iterations done inside of unsteady Adjoint: nothing to do"); unstack(); return -1; }
+            A->reverse();
+            const int oi = objective_index(solver);
+            if (oi >= 0) solver->domain->globals[oi] = A->objective;
+            logf(L_OUTPUT, "%8d it adjoint swept back over %zu iterations, Objective %.10lg", solver->iter, n, A->objective);
+        } else if (type == "steady") {
+            if (execute_internal()) return -1;
+            const int n = std::max(1, (int)every_iter);
+            A->drop_tape(); A->zero();
+            std::vector<int> pf = solver->parameter_fields();
+            std::vector<std::vector<double>> before(pf.size()), after(pf.size());
+            if (n > 1) A->steady(n - 1);
+            for (size_t k = 0; k < pf.size(); k++) get_adj_d(solver, pf[k], before[k]);
+            A->steady(1);
+            for (size_t k = 0; k < pf.size(); k++) {
+                get_adj_d(solver, pf[k], after[k]);
+                for (size_t i = 0; i < after[k].size(); i++) after[k][i] -= before[k][i];
+                set_adj_d(solver, pf[k], after[k]);
+            }
+            logf(L_OUTPUT, "%8d it steady adjoint: %d iterations", solver->iter, n);
+        } else { logf(L_ERROR, "Unknown type of adjoint in xml: %s", type.c_str()); return -1; }
+        unstack();
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("Adjoint", AcAdjoint)
+
+// <Objective Drag="1" PressureLoss="-0.5"/>: weights of SUM Globals in the objective (sets <Global>InObj in every zone)
+class AcObjective : public Action {
+  public:
+    int init() override {
+        Action::init();
+        const tclb_model_t *d = solver->model->d;
+        int nset = 0;
+        for (int g = 0; g < d->sum_globals; g++) {
+            std::string nm = d->globals[g].name;
+            if (nm == "Objective") continue;
+            const double w = node->has_attr(nm) ? atof(node->attr(nm).c_str()) : 0.0;
+            if (solver->model->find_zonesetting(nm + "InObj") < 0) continue;
+            solver->set_param(nm + "InObj", node->has_attr(nm) ? node->attr(nm) : "0", "", true, "");
+            if (w != 0.0) nset++;
+        }
+        if (nset == 0) logf(L_WARNING, "<Objective> names no Global of this model: the objective is zero");
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("Objective", AcObjective)
+
+// <ThresholdNow Level="0.5"/>: design variables become 0/1
+class AcThresholdNow : public Action {
+  public:
+    int init() override {
+        Action::init();
+        const double level = node->has_attr("Level") ? atof(node->attr("Level").c_str()) : 0.5;
+        std::vector<int> pf = solver->parameter_fields();
+        if (pf.empty()) { logf(L_ERROR, "No parameters defined!"); return -1; }
+        std::vector<char> mask = design_mask(solver);
+        size_t npar = 0;
+        for (int f : pf) {
+            std::vector<double> v;
+            get_field_d(solver, f, v);
+            for (size_t i = 0; i < v.size(); i++) if (mask[i]) { v[i] = v[i] > level ? 1.0 : 0.0; npar++; }
+            set_field_d(solver, f, v);
+        }
+        logf(L_OUTPUT, "Parameters: %zu", npar);
+        if (solver->model->find_setting("Threshold") >= 0) solver->set_param("Threshold", node->has_attr("Level") ? node->attr("Level") : "0.5", "", true, "");
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("ThresholdNow", AcThresholdNow)
+
+// <Threshold Levels="N"> children </Threshold>: run the children once per threshold level i/N on a thresholded copy of
+// the design, then put the design back
+class AcThreshold : public GenericAction {
+  public:
+    int init() override {
+        GenericAction::init();
+        const int levels = node->has_attr("Levels") ? atoi(node->attr("Levels").c_str()) : 5;
+        std::vector<int> pf = solver->parameter_fields();
+        if (pf.empty()) { logf(L_ERROR, "No parameters defined!"); return -1; }
+        std::vector<char> mask = design_mask(solver);
+        std::vector<std::vector<double>> orig(pf.size());
+        for (size_t k = 0; k < pf.size(); k++) get_field_d(solver, pf[k], orig[k]);
+        for (int i = 0; i <= levels; i++) {
+            const double level = (double)i / levels;
+            for (size_t k = 0; k < pf.size(); k++) {
+                std::vector<double> v = orig[k];
+                for (size_t j = 0; j < v.size(); j++) if (mask[j]) v[j] = v[j] > level ? 1.0 : 0.0;
+                set_field_d(solver, pf[k], v);
+            }
+            logf(L_OUTPUT, "Threshold level %lg", level);
+            if (execute_internal()) return -1;
+            unstack();
+        }
+        for (size_t k = 0; k < pf.size(); k++) set_field_d(solver, pf[k], orig[k]);
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("Threshold", AcThreshold)
+
+// <OptSolve Iterations="N" Descent="d">: one-shot optimisation, every iteration = one primal iteration (with the
+// Objective), one adjoint iteration around the new state and a descent step of the design variables,
+// clipped to [0,1] (reference ITER_OPT, src/cuda.cu.Rt:232-250: w += wb*Descent)
+class AcOptSolve : public GenericAction {
+  public:
+    int init() override {
+        GenericAction::init();
+        if (execute_internal()) return -1;
+        // step: Descent= attribute, else the model's Descent setting (<Param name="Descent">), else 1
+        double descent = 1.0;
+        const int ds = solver->model->find_setting("Descent");
+        if (node->has_attr("Descent")) descent = atof(node->attr("Descent").c_str());
+        else if (ds >= 0 && the_lattice(solver)->get_setting(ds) != 0.0) descent = the_lattice(solver)->get_setting(ds);
+        const bool maximise = node->attr("direction") == "max";
+        std::vector<int> pf = solver->parameter_fields();
+        if (pf.empty()) { logf(L_ERROR, "No parameters defined!"); return -1; }
+        std::vector<char> mask = design_mask(solver);
+        Adjoint *A = solver->need_adjoint();
+        A->drop_tape(); A->zero();
+        const int oi = objective_index(solver);
+        int ret = run_loop([&](int steps, int, bool) {
+            std::vector<double> p, g, zero;
+            for (int i = 0; i < steps; i++) {
+                solver->domain->iterate(1, false, true);
+                A->steady(1);
+                for (int f : pf) {
+                    get_field_d(solver, f, p);
+                    get_adj_d(solver, f, g);
+                    for (size_t j = 0; j < p.size(); j++)
+                        if (mask[j]) p[j] = std::min(1.0, std::max(0.0, p[j] + (maximise ? descent : -descent) * g[j]));
+                    set_field_d(solver, f, p);
+                    zero.assign(p.size(), 0.0);
+                    set_adj_d(solver, f, zero);
+                }
+            }
+            if (oi >= 0) logf(L_OUTPUT, "%8d it OptSolve Objective %.10lg", solver->iter, solver->domain->globals[oi]);
+        });
+        unstack();
+        return ret;
+    }
+};
+TCLB_REGISTER_HANDLER("OptSolve", AcOptSolve)
+
+// <FDTest Samples="K" Epsilon="e"> children </FDTest>: gradient of the objective accumulated by the children with respect to
+// K design variables, from the adjoint and from central differences (children re-run from the same state)
+class AcFDTest : public GenericAction {
+  public:
+    int init() override {
+        GenericAction::init();
+        const int samples = node->has_attr("Samples") ? atoi(node->attr("Samples").c_str()) : 5;
+        const double eps = node->has_attr("Epsilon") ? atof(node->attr("Epsilon").c_str()) : (solver->model->real_size() == 8 ? 1e-6 : 1e-3);
+        std::vector<int> pf = solver->parameter_fields();
+        if (pf.empty()) { logf(L_ERROR, "No parameters defined!"); return -1; }
+        Lattice *l = the_lattice(solver);
+        Adjoint *A = solver->need_adjoint();
+        const std::string state = solver->outpath + "_fdtest_state.raw";
+        const int iter0 = solver->iter, diter0 = solver->domain->iter;
+        l->save_raw(state);
+        auto restore = [&]() {
+            l->load_raw(state);
+            solver->iter = iter0; solver->domain->iter = diter0; l->iter = diter0;
+        };
+        auto run_children = [&](double &obj) -> int {
+            A->drop_tape(); A->zero(); A->objective = 0;
+            solver->recording = true;
+            int rc = execute_internal();
+            solver->recording = false;
+            unstack();
+            obj = A->objective;
+            return rc;
+        };
+        double J0 = 0;
+        if (run_children(J0)) return -1;
+        A->reverse();
+        std::vector<char> mask = design_mask(solver);
+        std::vector<size_t> cand;
+        for (size_t i = 0; i < mask.size(); i++) if (mask[i]) cand.push_back(i);
+        if (cand.empty()) { logf(L_ERROR, "FDTest: no node in the design space"); return -1; }
+        std::mt19937 rng(12345);
+        const int f = pf[0];
+        std::vector<double> grad;
+        get_adj_d(solver, f, grad);
+        double worst = 0;
+        logf(L_OUTPUT, "FDTest: objective %.12lg, %d samples, epsilon %lg", J0, samples, eps);
+        for (int k = 0; k < samples; k++) {
+            const size_t i = cand[rng() % cand.size()];
+            double Jp = 0, Jm = 0;
+            for (int sgn = +1; sgn >= -1; sgn -= 2) {
+                restore();
+                std::vector<double> p;
+                get_field_d(solver, f, p);
+                p[i] += sgn * eps;
+                set_field_d(solver, f, p);
+                double J = 0;
+                if (run_children(J)) return -1;
+                A->drop_tape();
+                (sgn > 0 ? Jp : Jm) = J;
+            }
+            const double fd = (Jp - Jm) / (2 * eps);
+            const double err = std::fabs(fd - grad[i]) / std::max(1e-300, std::max(std::fabs(fd), std::fabs(grad[i])));
+            worst = std::max(worst, err);
+            logf(L_OUTPUT, "FDTest: parameter %zu  adjoint %.10lg  finite difference %.10lg  relative difference %.3lg", i, grad[i], fd, err);
+        }
+        restore();
+        remove(state.c_str());
+        logf(L_OUTPUT, "FDTest: largest relative difference %.3lg", worst);
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("FDTest", AcFDTest)
+
+}  // namespace
+}  // namespace tclb

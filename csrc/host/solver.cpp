@@ -1,4 +1,5 @@
 #include "solver.h"
+#include "../core/adjoint.h"
 #include "../io/h5min.h"
 #include "../core/common.h"
 #include "../handlers/handler.h"
@@ -24,6 +25,7 @@ void NameSet::add_from_string(const std::string &s, char sep) {
 Solver::Solver(const SolverOptions &o) : opt(o) {}
 Solver::~Solver() {
     hands.clear();
+    adjoint.reset();
     sampler.reset();
     geometry.clear();
     domain.reset();
@@ -270,6 +272,23 @@ int Solver::write_vtk(const std::string &name, const NameSet &what, const Box &r
             l->get_quantity(q, loc, tmp.data(), 1 / v);
             vtk.write_field(d->quantities[q].name, tmp.data(), model->real_size(), rtype, comp);
         }
+        // adjoint of a field: <VTK what="...,<field>_adj"/> after an <Adjoint> element (name with [ ] removed)
+        if (adjoint) {
+            for (int f = 0; f < d->n_fields; f++) {
+                std::string nm = d->fields[f].name;
+                nm.erase(std::remove_if(nm.begin(), nm.end(), [](char c) { return c == '[' || c == ']' || c == ' '; }), nm.end());
+                nm += "_adj";
+                if (!what.explicitly_in(nm)) continue;
+                const int rs = model->real_size();
+                std::vector<char> full((size_t)l->nx * l->ny * l->nz * rs), tmp(n * rs);
+                adjoint->get_field(f, full.data());
+                for (int z = 0; z < loc.nz; z++)
+                    for (int y = 0; y < loc.ny; y++)
+                        memcpy(tmp.data() + (((size_t)z * loc.ny + y) * loc.nx) * rs,
+                               full.data() + ((((size_t)(z + loc.z0)) * l->ny + (y + loc.y0)) * l->nx + loc.x0) * rs, (size_t)loc.nx * rs);
+                vtk.write_field(nm, tmp.data(), rs, rtype, 1);
+            }
+        }
         vtk.finish();
         vtk.close();
     }
@@ -495,7 +514,21 @@ void Solver::set_param(const std::string &par, const std::string &value, const s
 }
 
 // ---------------------------------------------------------------- iteration ----
+Adjoint *Solver::need_adjoint() {
+    if (!adjoint) adjoint.reset(new Adjoint(domain.get()));
+    return adjoint.get();
+}
+std::vector<int> Solver::parameter_fields() const {
+    std::vector<int> out;
+    for (int f = 0; f < model->d->n_fields; f++) if (model->d->fields[f].parameter) out.push_back(f);
+    return out;
+}
 void Solver::iterate(int n, int type) {
+    if (recording) {                   // inside <Adjoint type="unsteady">: Globals every iteration, inputs on the tape
+        need_adjoint()->record(n);
+        monitor();
+        return;
+    }
     bool last_glob = (type & ITER_LASTGLOB) != 0;
     if (type & ITER_INTEG) last_glob = false;
     if (sampler && sampler->active()) {

@@ -21,6 +21,7 @@ namespace tclb {
 
 class Handler;
 class Sampler;
+class Adjoint;
 
 // "what=" lists (reference src/utils.h name_set)
 struct NameSet {
@@ -103,6 +104,11 @@ class Solver {
     void set_param(const std::string &name, const std::string &value, const std::string &zone, bool permissive, const std::string &gauge);
     // ---- iteration ----
     void iterate(int n, int type);
+    // ---- adjoint (csrc/core/adjoint.h): while `recording`, iterate() keeps every iteration's input on the tape ----
+    std::unique_ptr<Adjoint> adjoint;
+    bool recording = false;
+    Adjoint *need_adjoint();           // created on first use (loads the _ad companion of the model library)
+    std::vector<int> parameter_fields() const;     // fields declared with parameter=TRUE (design variables)
     void iterate_action(int action, int n, int type);
     void monitor(bool force = false);
     bool has_nan(const NameSet &what, const Box &region);

@@ -255,7 +255,8 @@ def build_from_dir(model_dir: str, name: Optional[str] = None, precision: str = 
 REFERENCE_ROOT = Path(os.environ.get("TCLB_REFERENCE", "/root/reference"))
 REFERENCE_MODELS = ["multiphase/d3q27_pf_velocity", "flow/d2q9", "flow/d3q19", "flow/d3q27_cumulant", "heat/d3q19_heat",
                     "electrokinetic/d2q9_poison_boltzmann", "electrokinetic/d2q9_npe_guo", "multiphase/d2q9_kuper",
-                    "particles/d3q27_PSM:NEBB"]            # "<directory>[:<option>,...]"
+                    "particles/d3q27_PSM:NEBB", "optimization/d2q9_adj"]            # "<directory>[:<option>,...]"
+REFERENCE_ADJOINT = ["ref_d2q9_adj"]             # libraries that also get their adjoint companion (build_adjoint_lib)
 
 
 def build_reference_models(precisions=("float", "double"), verbose=False) -> List[Path]:
@@ -271,6 +272,9 @@ def build_reference_models(precisions=("float", "double"), verbose=False) -> Lis
             out.append(build_from_dir(str(d), precision=p, options={o: True for o in optlist.split(",") if o}))
             if verbose:
                 print(f"built {out[-1]}")
+            name = out[-1].name[len("libtclb_"):-len(f"_{p}.so")]
+            if name in REFERENCE_ADJOINT:
+                out.append(build_adjoint_lib(name, p))
     return out
 
 
@@ -282,6 +286,15 @@ def build_all(models: Optional[List[str]] = None, precisions=("float", "double")
         futs = {ex.submit(build_model_lib, m, p, force, verbose): (m, p) for m, p in tasks}
         for f in cf.as_completed(futs):
             f.result()
+    # adjoint companions (dual-number build) of the models the adjoint tests and examples use
+    for m in ADJOINT_MODELS:
+        if m in models:
+            for p in precisions:
+                if p in ("float", "double"):
+                    build_adjoint_lib(m, p, force=force)
+
+
+ADJOINT_MODELS = ["d2q9", "d3q19"]
 
 
 def main(argv=None) -> int:

@@ -402,6 +402,10 @@ class ModelDef:
             self.AddSetting(name="Descent", comment="Optimization Descent", adjoint=True)
             self.AddSetting(name="GradientSmooth", comment="Gradient smoothing in OptSolve", adjoint=True)
             self.AddGlobal(name="AdjointRes", comment="square L2 norm of adjoint change", adjoint=True)
+        elif getattr(self, "adjoint_requested", 0) == 1:
+            # primal build of an ADJOINT=1 model: its case files still set the optimisation step (<OptSolve> reads it)
+            self.AddSetting(name="Descent", comment="Optimization Descent", adjoint=True)
+            self.AddSetting(name="GradientSmooth", comment="Gradient smoothing in OptSolve", adjoint=True)
         self.AddGlobal(name="Objective", comment="Objective function")
         c = sorted([g for g in self.globals if g.op != "SUM"], key=lambda g: g.op)
         b = [g for g in self.globals if g.name == "Objective"]

@@ -88,3 +88,42 @@ def test_adjoint_needs_its_library(tmp_path):
 def test_adjoint_gradient_matches_finite_differences_gpu():
     _check_against_fd("cuda", "double", 1e-6, 1e-6)
     _check_against_fd("cuda", "float", 2e-3, 5e-2)
+
+
+def _run_adj_case(reference_dir, tclb_bin, tmp_path, backend_flag, precision):
+    """The reference's own topology-optimisation model (models/optimization/d2q9_adj, lowered by the front-end, primal
+    part + dual-number adjoint) through <Objective>, <FDTest>, <Adjoint>, <VTK what=w_adj>, <OptSolve>, <ThresholdNow>."""
+    import os
+    import re
+    import shutil
+    import subprocess
+    if reference_dir is not None:
+        build.build_from_dir(os.path.join(reference_dir, "models/optimization/d2q9_adj"), precision=precision)
+        build.build_adjoint_lib("ref_d2q9_adj", precision)
+    elif not (build.LIBDIR / f"libtclb_ref_d2q9_adj_{precision}_ad.so").exists():
+        pytest.skip("ref_d2q9_adj libraries were not built (reference tree not mounted at build time)")
+    here = os.path.dirname(os.path.abspath(__file__))
+    shutil.copy(os.path.join(here, "cases", "adj_drag_small.xml"), tmp_path / "adj.xml")
+    r = subprocess.run([tclb_bin, backend_flag, "--precision", precision, "ref_d2q9_adj", "adj.xml"], cwd=tmp_path,
+                       capture_output=True, text=True, timeout=600)
+    out = r.stdout + r.stderr
+    assert r.returncode == 0, out[-3000:]
+    worst = float(re.search(r"FDTest: largest relative difference ([-+.eE0-9]+)", out).group(1))
+    sweep = re.search(r"adjoint swept back over (\d+) iterations, Objective ([-+.eE0-9]+)", out)
+    fd_obj = float(re.search(r"FDTest: objective ([-+.eE0-9]+)", out).group(1))
+    assert int(sweep.group(1)) == 8
+    assert abs(float(sweep.group(2)) - fd_obj) <= 1e-6 * abs(fd_obj)      # same 8 iterations from the same state
+    assert "Parameters: 192" in out                                       # the 16x12 design space was thresholded
+    vti = [f for f in os.listdir(tmp_path / "output") if f.endswith(".vti")]
+    assert vti and b"w_adj" in open(tmp_path / "output" / vti[0], "rb").read()
+    return worst
+
+
+def test_reference_adjoint_model_fdtest_and_optsolve_cpu(reference_dir, tclb_bin, tmp_path):
+    assert _run_adj_case(reference_dir, tclb_bin, tmp_path, "--cpu", "double") < 1e-5
+
+
+@pytest.mark.gpu
+def test_reference_adjoint_model_fdtest_and_optsolve_gpu(tclb_bin, tmp_path):
+    # the libraries travel with the tree; the reference checkout itself is not on the GPU box
+    assert _run_adj_case(None, tclb_bin, tmp_path, "--gpu", "double") < 1e-5
