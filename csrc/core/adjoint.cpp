@@ -1,6 +1,8 @@
 #include "adjoint.h"
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include "common.h"
@@ -41,6 +43,8 @@ Adjoint::Adjoint(Domain *dom) : dom_(dom), lat_(nullptr) {
     if (info(&rs, &dirs, &nf) != TCLB_ABI_VERSION) fail("adjoint: %s was built for another ABI version (rebuild it)", p.c_str());
     if (rs != m->real_size() || nf != m->d->n_fields) fail("adjoint: %s does not match the primal library", p.c_str());
     rs_ = rs;
+    dirs_ = dirs;
+    sfn_ = (settings_fn)dlsym(lib_, "tclb_model_adjoint_settings");
     bytes_ = (size_t)m->d->n_fields * lat_->plane_elems * rs_;
     const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
     for (int i = 0; i < 2; i++) { adj_[i] = alloc(bytes_, dev); fill_zero(adj_[i]); }
@@ -51,6 +55,7 @@ Adjoint::~Adjoint() {
     drop_tape();
     const bool dev = lat_ && lat_->backend == TCLB_BACKEND_CUDA;
     for (int i = 0; i < 2; i++) if (adj_[i]) release(adj_[i], dev);
+    if (sg_dev_) cudaFree(sg_dev_);
     if (lib_) dlclose(lib_);
 }
 void *Adjoint::alloc(size_t bytes, bool device) const {
@@ -107,6 +112,7 @@ void Adjoint::step(const void *primal_in, int iter) {
     fill_zero(in);
     if (lat_->backend == TCLB_BACKEND_CUDA) ADJ_CUDA(cudaSetDevice(lat_->device));
     if (fn_(stage_, &L, out, in) != 0) fail("adjoint stage failed: %s", err_());
+    if (!sg_which_.empty()) settings_pass(L, out);
     if (tclb_adjoint_fold_ghosts(in, rs_, lat_->backend == TCLB_BACKEND_CUDA, dom_->model->d->n_fields, lat_->nx, lat_->ny, lat_->nz,
                                  lat_->gy, lat_->gz, lat_->stream) != 0)
         fail("adjoint: ghost fold failed");
@@ -134,6 +140,54 @@ void Adjoint::reverse() {
 void Adjoint::steady(int n) {
     for (int i = 0; i < n; i++) step(lat_->snap_ptr(lat_->cur), lat_->iter);
     if (lat_->backend == TCLB_BACKEND_CUDA) ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
+}
+void Adjoint::want_setting_gradients(const std::vector<int> &settings) {
+    if (!sfn_) fail("adjoint: the adjoint library has no settings entry point (rebuild it)");
+    const tclb_model_t *d = dom_->model->d;
+    sg_which_.clear();
+    for (int s : settings) {
+        int guard = 0;
+        while (s >= 0 && s < d->n_settings && guard++ < 64) {
+            if (std::find(sg_which_.begin(), sg_which_.end(), s) == sg_which_.end()) sg_which_.push_back(s);
+            s = d->settings[s].derived_target;
+        }
+    }
+    sg_sum_.assign(sg_which_.size(), 0.0);
+    if (lat_->backend == TCLB_BACKEND_CUDA && !sg_which_.empty()) {
+        if (sg_dev_) cudaFree(sg_dev_);
+        ADJ_CUDA(cudaSetDevice(lat_->device));
+        ADJ_CUDA(cudaMalloc((void **)&sg_dev_, sizeof(double) * (sg_which_.size() + dirs_)));
+        ADJ_CUDA(cudaMemset(sg_dev_, 0, sizeof(double) * (sg_which_.size() + dirs_)));
+    }
+}
+void Adjoint::settings_pass(const tclb_launch_t &L, const void *adj_out) {
+    const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+    for (size_t o = 0; o < sg_which_.size(); o += dirs_) {
+        const int n = (int)std::min((size_t)dirs_, sg_which_.size() - o);
+        double *dst = dev ? sg_dev_ + o : sg_sum_.data() + o;
+        if (sfn_(stage_, &L, adj_out, sg_which_.data() + o, n, dst) != 0) fail("adjoint settings pass failed: %s", err_());
+    }
+}
+double Adjoint::setting_gradient(int setting) {
+    const tclb_model_t *d = dom_->model->d;
+    if (lat_->backend == TCLB_BACKEND_CUDA && sg_dev_) {
+        ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
+        ADJ_CUDA(cudaMemcpy(sg_sum_.data(), sg_dev_, sizeof(double) * sg_sum_.size(), cudaMemcpyDeviceToHost));
+    }
+    // total derivative along the chain of derived settings: dJ/dv_i = partial_i + f_i'(v_i) * dJ/dv_target
+    double total = 0, factor = 1;
+    int s = setting, guard = 0;
+    while (s >= 0 && s < d->n_settings && guard++ < 64) {
+        auto it = std::find(sg_which_.begin(), sg_which_.end(), s);
+        if (it == sg_which_.end()) fail("adjoint: gradient of setting %s was not requested", d->settings[s].name);
+        total += factor * sg_sum_[it - sg_which_.begin()];
+        const tclb_setting_t &S = d->settings[s];
+        if (S.derived_target < 0 || !S.derive) break;
+        const double v = lat_->get_setting(s), h = std::max(1e-7, std::fabs(v) * 1e-6);
+        factor *= (S.derive(v + h) - S.derive(v - h)) / (2 * h);
+        s = S.derived_target;
+    }
+    return total;
 }
 // interior <-> dense copies (adjoint buffers have the snapshot layout [field][NZ][NY][nx] in real_t)
 void Adjoint::get_field(int field, void *dst) const {

@@ -31,7 +31,17 @@ class Adjoint {
     void set_field(int field, const void *src_real);    // seed (e.g. d(cost)/d(final state))
     double dot_field(int field, const void *dir_real) const;   // sum adjoint * dir over the interior
     int real_size() const { return rs_; }
+    // ---- gradients with respect to (non-zonal) settings, accumulated by reverse()/steady() ----
+    void want_setting_gradients(const std::vector<int> &settings);   // call before record(); clears the sums
+    double setting_gradient(int setting);        // total derivative: follows the derived-settings chain (nu -> omega ...)
   private:
+    typedef int (*settings_fn)(int, const tclb_launch_t *, const void *, const int *, int, double *);
+    settings_fn sfn_ = nullptr;
+    int dirs_ = 4;
+    std::vector<int> sg_which_;          // requested settings + everything derived from them
+    std::vector<double> sg_sum_;         // direct partial derivatives, same order
+    double *sg_dev_ = nullptr;           // device accumulator (CUDA backend)
+    void settings_pass(const tclb_launch_t &L, const void *adj_out);
     typedef int (*stage_fn)(int, const tclb_launch_t *, const void *, void *);
     typedef const char *(*err_fn)(void);
     struct Frame { void *data; bool on_device; int iter; };

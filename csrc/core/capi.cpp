@@ -329,6 +329,32 @@ int tclb_adjoint_reverse(tclb_adjoint_h *a) { GUARD_BEGIN a->a->reverse(); GUARD
 int tclb_adjoint_steady(tclb_adjoint_h *a, int n) { GUARD_BEGIN a->a->steady(n); GUARD_END_INT }
 int tclb_adjoint_zero(tclb_adjoint_h *a) { GUARD_BEGIN a->a->zero(); a->a->objective = 0; GUARD_END_INT }
 double tclb_adjoint_objective(tclb_adjoint_h *a) { return a->a->objective; }
+int tclb_adjoint_want_setting(tclb_adjoint_h *a, tclb_domain_h *h, const char *names_csv) {
+    GUARD_BEGIN
+    std::vector<int> idx;
+    std::string all = names_csv ? names_csv : "";
+    size_t p0 = 0;
+    while (p0 <= all.size()) {
+        size_t c = all.find(',', p0);
+        std::string nm = all.substr(p0, c == std::string::npos ? std::string::npos : c - p0);
+        if (!nm.empty()) {
+            int i = h->d->model->find_setting(nm);
+            if (i < 0) fail("unknown (non-zonal) setting %s", nm.c_str());
+            idx.push_back(i);
+        }
+        if (c == std::string::npos) break;
+        p0 = c + 1;
+    }
+    a->a->want_setting_gradients(idx);
+    GUARD_END_INT
+}
+int tclb_adjoint_setting_gradient(tclb_adjoint_h *a, tclb_domain_h *h, const char *name, double *out) {
+    GUARD_BEGIN
+    int i = h->d->model->find_setting(name);
+    if (i < 0) fail("unknown (non-zonal) setting %s", name);
+    *out = a->a->setting_gradient(i);
+    GUARD_END_INT
+}
 int tclb_adjoint_get_field(tclb_adjoint_h *a, tclb_domain_h *h, const char *f, void *dst) {
     GUARD_BEGIN
     int i = h->d->model->find_field(f);

@@ -118,6 +118,10 @@ int tclb_adjoint_reverse(tclb_adjoint_h *);
 int tclb_adjoint_steady(tclb_adjoint_h *, int n);
 int tclb_adjoint_zero(tclb_adjoint_h *);
 double tclb_adjoint_objective(tclb_adjoint_h *);
+/* gradients with respect to non-zonal settings (comma separated names; call before record()); the value returned is
+ * the total derivative, following the derived-settings chain (e.g. nu -> omega) */
+int tclb_adjoint_want_setting(tclb_adjoint_h *, tclb_domain_h *, const char *names_csv);
+int tclb_adjoint_setting_gradient(tclb_adjoint_h *, tclb_domain_h *, const char *name, double *out);
 int tclb_adjoint_get_field(tclb_adjoint_h *, tclb_domain_h *, const char *field, void *dst_real);
 int tclb_adjoint_set_field(tclb_adjoint_h *, tclb_domain_h *, const char *field, const void *src_real);
 

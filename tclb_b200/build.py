@@ -180,6 +180,9 @@ def build_model_lib(variant: str, precision: str = "float", force: bool = False,
     return target
 
 
+_CUSTOM_MODELS: dict = {}      # library name -> how to load its ModelDef again (models built from a directory)
+
+
 def build_adjoint_lib(variant: str, precision: str = "double", dirs: int = 4, force: bool = False) -> Path:
     """The adjoint companion of a model library: the same generated source compiled with -DTCLB_AD (node code in dual
     numbers, csrc/kernels/tclb_dual.h), exporting ``tclb_model_adjoint_stage``.  The runtime loads
@@ -188,9 +191,18 @@ def build_adjoint_lib(variant: str, precision: str = "double", dirs: int = 4, fo
     if precision not in ("float", "double"):
         raise ValueError("adjoint libraries use plain float/double storage")
     LIBDIR.mkdir(parents=True, exist_ok=True)
-    src = GENDIR / f"{variant}.cu"
-    if not (variant.startswith("ref_") and src.exists()):
-        src = generate_model(variant)
+    GENDIR.mkdir(parents=True, exist_ok=True)
+    from .gen.emit import emit_model_source
+    src = GENDIR / f"{variant}_ad.cu"
+    with _GEN_LOCK:
+        if variant in _CUSTOM_MODELS:
+            m = _CUSTOM_MODELS[variant]()
+        else:
+            from .models import build_model
+            m = build_model(variant)
+        text = emit_model_source(m, variant, adjoint=True)
+        if not src.exists() or src.read_text() != text:
+            src.write_text(text)
     target = LIBDIR / f"libtclb_{variant}_{precision}_ad.so"
     hdrs = [ROOT / "include" / "tclb_model_abi.h", ROOT / "csrc" / "kernels" / "tclb_node_rt.h", ROOT / "csrc" / "kernels" / "tclb_dual.h"]
     extra = ["-DTCLB_AD", f"-DTCLB_AD_DIRS={int(dirs)}"]
@@ -248,6 +260,7 @@ def build_from_dir(model_dir: str, name: Optional[str] = None, precision: str = 
         m = rfrontend.load_model(model_dir, name=name, options=options)
     on = [k for k, v in (options or {}).items() if v]
     lib = libname or "ref_" + "_".join([m.name] + on)
+    _CUSTOM_MODELS[lib] = lambda: rfrontend.load_model(model_dir, name=name, options=options)
     return build_custom(m, lib, precision)
 
 

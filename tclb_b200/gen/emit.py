@@ -193,8 +193,10 @@ struct ParticleRange {
 """
 
 
-def emit_model_source(m: ModelDef, libname: str) -> str:
-    """Return the text of the generated .cu file (precision chosen by -DTCLB_DOUBLE)."""
+def emit_model_source(m: ModelDef, libname: str, adjoint: bool = False) -> str:
+    """Return the text of the generated .cu file (precision chosen by -DTCLB_DOUBLE).  With `adjoint` the source also
+    carries the section compiled under -DTCLB_AD (the dual-number adjoint, see adjoint.cu.in); the ordinary source leaves
+    it out so that work on the adjoint does not touch the primal libraries."""
     m.finalize()
     nf, nd = len(m.fields), len(m.densities)
     ns, nzs, ng, nq = len(m.settings), len(m.zonesettings), len(m.globals), len(m.quantities)
@@ -568,6 +570,7 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
 
     # ---- adjoint build: seeds, collection and scatter per stage (see adjoint.cu.in) ----
     A("#ifdef TCLB_AD")
+    ad_mark = len(L)
     A("TCLB_HD void ad_add(base_t *p, base_t v);")
     loaded = [[(di, d) for di, d in enumerate(m.densities) if d.load.get(s.name)] for s in m.stages]
     A("TCLB_HD int ad_inputs_of_stage(int s) {\n    switch (s) {")
@@ -609,8 +612,17 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     for si in range(len(m.stages)):
         A(f"    case {si}: return run_adjoint_stage<{si}>(a, L, (const base_t *)adj_out, (base_t *)adj_in);")
     A('    default: set_error("bad stage"); return -1;\n    }\n}')
+    A('extern "C" int tclb_model_adjoint_settings(int stage, const tclb_launch_t *L, const void *adj_out, const int *which, int n, double *grad) {')
+    A("    KArgs a; int bx, by; fill_args(a, L, bx, by);")
+    A("    switch (stage) {")
+    for si in range(len(m.stages)):
+        A(f"    case {si}: return run_adjoint_settings<{si}>(a, L, (const base_t *)adj_out, which, n, grad);")
+    A('    default: set_error("bad stage"); return -1;\n    }\n}')
     A('extern "C" const char *tclb_model_adjoint_error(void) { return g_error; }')
     A(f'extern "C" int tclb_model_adjoint_info(int *real_size, int *dirs, int *n_fields) {{ *real_size = (int)sizeof(base_t); *dirs = TCLB_AD_DIRS; *n_fields = N_FIELDS; return TCLB_ABI_VERSION; }}')
+    if not adjoint:
+        del L[ad_mark:]
+        A('#error "this source was generated without the adjoint section (emit_model_source(..., adjoint=True))"')
     A("#else  // !TCLB_AD")
 
     # ---- dispatch tables ----

@@ -170,6 +170,8 @@ def core():
         "tclb_adjoint_zero": [C.c_void_p],
         "tclb_adjoint_objective": [C.c_void_p],
         "tclb_adjoint_get_field": [C.c_void_p, C.c_void_p, C.c_char_p, C.c_void_p],
+        "tclb_adjoint_want_setting": [C.c_void_p, C.c_void_p, C.c_char_p],
+        "tclb_adjoint_setting_gradient": [C.c_void_p, C.c_void_p, C.c_char_p, C.POINTER(C.c_double)],
         "tclb_adjoint_set_field": [C.c_void_p, C.c_void_p, C.c_char_p, C.c_void_p],
     }.items():
         getattr(lib, fn).argtypes = args
@@ -471,6 +473,15 @@ class Adjoint:
     @property
     def objective(self) -> float:
         return float(self.lib.tclb_adjoint_objective(self.h))
+
+    def want_setting_gradients(self, names):
+        """ask for dObjective/d(setting) of these non-zonal settings (before record())"""
+        _check(self.lib.tclb_adjoint_want_setting(self.h, self.domain.h, ",".join(names).encode()))
+
+    def setting_gradient(self, name: str) -> float:
+        out = C.c_double(0.0)
+        _check(self.lib.tclb_adjoint_setting_gradient(self.h, self.domain.h, name.encode(), C.byref(out)))
+        return out.value
 
     def get_field(self, name: str) -> np.ndarray:
         nx, ny, nz = self.domain.shape

@@ -127,3 +127,34 @@ def test_reference_adjoint_model_fdtest_and_optsolve_cpu(reference_dir, tclb_bin
 def test_reference_adjoint_model_fdtest_and_optsolve_gpu(tclb_bin, tmp_path):
     # the libraries travel with the tree; the reference checkout itself is not on the GPU box
     assert _run_adj_case(None, tclb_bin, tmp_path, "--gpu", "double") < 1e-5
+
+
+def test_adjoint_setting_gradients_match_finite_differences_cpu():
+    """dObjective/d(setting) from the settings pass of the adjoint, including the derived chain Viscosity -> omega"""
+    build.build_model_lib("d2q9", "double")
+    build.build_adjoint_lib("d2q9", "double")
+    m = Model("d2q9", "double")
+    shape, n = (24, 12, 1), 6
+    d = _channel(m, shape, "cpu")
+    fields = list(m.fields)
+    base = {f: d.get_field(f) for f in fields}
+    names = ["Viscosity", "GravitationX"]
+    values = {"Viscosity": 0.05, "GravitationX": 1e-4}
+    adj = Adjoint(d)
+    adj.want_setting_gradients(names)
+    adj.record(n)
+    adj.reverse()
+    for name in names:
+        g = adj.setting_gradient(name)
+        eps = 1e-6 * max(1.0, abs(values[name]) * 1e3)
+        J = []
+        for sign in (+1, -1):
+            d.set_setting(name, values[name] + sign * eps)
+            for f in fields:
+                d.set_field(f, base[f])
+            J.append(_objective_sum(d, n))
+        d.set_setting(name, values[name])
+        fd = (J[0] - J[1]) / (2 * eps)
+        assert g != 0.0 and abs(fd - g) <= 1e-5 * max(abs(fd), abs(g)), (name, fd, g)
+    adj.close()
+    d.close()

@@ -12,8 +12,10 @@ from tclb_b200 import build  # noqa: E402
 from tclb_b200.gen import rfrontend  # noqa: E402
 from tclb_b200.gen.emit import emit_model_source  # noqa: E402
 
-root = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
-only = sys.argv[2:]
+AD = "--ad" in sys.argv          # also check the adjoint (dual-number) build of every model that compiles
+args = [a for a in sys.argv[1:] if a != "--ad"]
+root = args[0] if args else "/root/reference"
+only = args[1:]
 out = build.ROOT / "build" / "gen_try"
 out.mkdir(parents=True, exist_ok=True)
 OPTS = {"d2q9_scmp": {"Kupershtokh": True}, "d2q9_reaction_diffusion_system": {"AllenCahn": True}, "d3q27_PSM": {"NEBB": True}}
@@ -42,6 +44,12 @@ def compile_one(job):
            "-I", str(build.ROOT / "csrc" / "kernels"), "-I", "/usr/local/cuda/include", str(src)]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode == 0:
+        if AD:
+            r2 = subprocess.run(cmd[:-1] + ["-DTCLB_AD", cmd[-1]], capture_output=True, text=True)
+            if r2.returncode != 0:
+                errs = [l for l in r2.stderr.splitlines() if "error" in l]
+                return name, "ok (adjoint build FAILED: " + (errs[0][-140:] if errs else "?") + ")"
+            return name, "ok + adjoint build"
         return name, "ok"
     errs = [l for l in r.stderr.splitlines() if "error" in l]
     return name, f"compile FAILED ({len(errs)} errors): " + (errs[0][-170:] if errs else r.stderr[-170:])
@@ -53,5 +61,7 @@ with cf.ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
 good = 0
 for name in sorted(status):
     print(f"{name:40s} {status[name]}")
-    good += status[name] == "ok"
+    good += status[name].startswith("ok")
 print(good, "of", len(status), "models lower and compile")
+if AD:
+    print(sum(1 for v in status.values() if v == "ok + adjoint build"), "of them also compile as an adjoint (dual-number) build")
