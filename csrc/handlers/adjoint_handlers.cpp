@@ -178,7 +178,7 @@ class AcThreshold : public GenericAction {
 };
 TCLB_REGISTER_HANDLER("Threshold", AcThreshold)
 
-// <OptSolve Iterations="N" Descent="d">: one-shot optimisation, every iteration = one primal iteration (with the
+// <OptSolve Iterations="N" Descent="d" [direction="min"]>: one-shot optimisation, every iteration = one primal iteration (with the
 // Objective), one adjoint iteration around the new state and a descent step of the design variables,
 // clipped to [0,1] (reference ITER_OPT, src/cuda.cu.Rt:232-250: w += wb*Descent)
 class AcOptSolve : public GenericAction {
@@ -191,7 +191,8 @@ class AcOptSolve : public GenericAction {
         const int ds = solver->model->find_setting("Descent");
         if (node->has_attr("Descent")) descent = atof(node->attr("Descent").c_str());
         else if (ds >= 0 && the_lattice(solver)->get_setting(ds) != 0.0) descent = the_lattice(solver)->get_setting(ds);
-        const bool maximise = node->attr("direction") == "max";
+        // the reference's descent step is w += wb*Descent: the objective is MAXIMISED (DragInObj = -1 minimises the drag)
+        const bool maximise = node->attr("direction") != "min";
         std::vector<int> pf = solver->parameter_fields();
         if (pf.empty()) { logf(L_ERROR, "No parameters defined!"); return -1; }
         std::vector<char> mask = design_mask(solver);
@@ -288,6 +289,86 @@ class AcFDTest : public GenericAction {
     }
 };
 TCLB_REGISTER_HANDLER("FDTest", AcFDTest)
+
+// <Optimize MaxEvaluations="N" [method="GD"] [Step="s"]> children </Optimize>: maximise the objective accumulated by the
+// children over the design variables, bounds [0,1].  The reference hands this to NLopt (MMA, L-BFGS, COBYLA ...,
+// src/Handlers/acOptimize.cpp.Rt); NLopt is not available here, so the built-in method is projected gradient ascent
+// with backtracking on the step: every evaluation = children from the same start state on the tape + reverse sweep.
+class AcOptimize : public GenericAction {
+  public:
+    int init() override {
+        GenericAction::init();
+        const std::string method = node->has_attr("method") ? node->attr("method") : "GD";
+        if (method != "GD") { logf(L_ERROR, "Unknown Method in Optimize: %s (this build has GD; NLopt methods are not available)", method.c_str()); return -1; }
+        if (node->has_attr("Material")) logf(L_WARNING, "Optimize: the Material constraint is not implemented by the GD method");
+        const int max_eval = node->has_attr("MaxEvaluations") ? atoi(node->attr("MaxEvaluations").c_str()) : 20;
+        double step = node->has_attr("Step") ? atof(node->attr("Step").c_str()) : 1.0;
+        std::vector<int> pf = solver->parameter_fields();
+        if (pf.empty()) { logf(L_ERROR, "Error: No parameters defined!"); return -1; }
+        Lattice *l = the_lattice(solver);
+        Adjoint *A = solver->need_adjoint();
+        std::vector<char> mask = design_mask(solver);
+        const std::string state = solver->outpath + "_optimize_state.raw";
+        const int iter0 = solver->iter, diter0 = solver->domain->iter;
+        l->save_raw(state);
+        size_t npar = 0;
+        for (char c : mask) npar += c ? pf.size() : 0;
+        logf(L_NOTICE, "Parameters in optimization: %zu", npar);
+        std::vector<std::vector<double>> x(pf.size()), g(pf.size()), trial(pf.size());
+        for (size_t k = 0; k < pf.size(); k++) get_field_d(solver, pf[k], x[k]);
+        auto evaluate = [&](const std::vector<std::vector<double>> &p, double &obj, bool want_grad) -> int {
+            l->load_raw(state);
+            solver->iter = iter0; solver->domain->iter = diter0; l->iter = diter0;
+            for (size_t k = 0; k < pf.size(); k++) set_field_d(solver, pf[k], p[k]);
+            A->drop_tape(); A->zero(); A->objective = 0;
+            solver->recording = true;
+            int rc = execute_internal();
+            solver->recording = false;
+            unstack();
+            if (rc) return rc;
+            obj = A->objective;
+            if (want_grad) { A->reverse(); for (size_t k = 0; k < pf.size(); k++) get_adj_d(solver, pf[k], g[k]); }
+            else A->drop_tape();
+            return 0;
+        };
+        double best = 0;
+        int evals = 0;
+        if (evaluate(x, best, true)) return -1;
+        evals++;
+        logf(L_OUTPUT, "Optimize: evaluation %d objective %.10lg", evals, best);
+        while (evals < max_eval) {
+            double gmax = 0;
+            for (size_t k = 0; k < pf.size(); k++) for (size_t i = 0; i < g[k].size(); i++) if (mask[i]) gmax = std::max(gmax, std::fabs(g[k][i]));
+            if (gmax == 0) { logf(L_OUTPUT, "Optimize: zero gradient, stopping"); break; }
+            bool improved = false;
+            while (evals < max_eval && !improved) {
+                // step scaled so that the largest change of a design variable is `step`
+                for (size_t k = 0; k < pf.size(); k++) {
+                    trial[k] = x[k];
+                    for (size_t i = 0; i < trial[k].size(); i++)
+                        if (mask[i]) trial[k][i] = std::min(1.0, std::max(0.0, x[k][i] + step * g[k][i] / gmax));
+                }
+                double obj = 0;
+                std::vector<std::vector<double>> gkeep = g;
+                if (evaluate(trial, obj, true)) return -1;
+                evals++;
+                if (obj > best) { best = obj; x = trial; improved = true; step *= 1.5; }
+                else { g = gkeep; step *= 0.5; }
+                logf(L_OUTPUT, "Optimize: evaluation %d objective %.10lg %s (step %lg)", evals, obj, improved ? "accepted" : "rejected", step);
+                if (step < 1e-8) break;
+            }
+            if (!improved) break;
+        }
+        // leave the solver at the start state with the best design
+        l->load_raw(state);
+        solver->iter = iter0; solver->domain->iter = diter0; l->iter = diter0;
+        for (size_t k = 0; k < pf.size(); k++) set_field_d(solver, pf[k], x[k]);
+        remove(state.c_str());
+        logf(L_OUTPUT, "Optimize: best objective %.10lg after %d evaluations", best, evals);
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("Optimize", AcOptimize)
 
 }  // namespace
 }  // namespace tclb

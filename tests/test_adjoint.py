@@ -113,6 +113,9 @@ def _run_adj_case(reference_dir, tclb_bin, tmp_path, backend_flag, precision):
     fd_obj = float(re.search(r"FDTest: objective ([-+.eE0-9]+)", out).group(1))
     assert int(sweep.group(1)) == 8
     assert abs(float(sweep.group(2)) - fd_obj) <= 1e-6 * abs(fd_obj)      # same 8 iterations from the same state
+    ev = [float(v) for v in re.findall(r"Optimize: evaluation \d+ objective ([-+.eE0-9]+)", out)]
+    best = float(re.search(r"Optimize: best objective ([-+.eE0-9]+)", out).group(1))
+    assert len(ev) >= 2 and best >= ev[0] and best == max(ev)              # maximised, never worse than the start
     assert "Parameters: 192" in out                                       # the 16x12 design space was thresholded
     vti = [f for f in os.listdir(tmp_path / "output") if f.endswith(".vti")]
     assert vti and b"w_adj" in open(tmp_path / "output" / vti[0], "rb").read()
