@@ -48,11 +48,17 @@ Adjoint::Adjoint(Domain *dom) : dom_(dom), lat_(nullptr) {
     bytes_ = (size_t)m->d->n_fields * lat_->plane_elems * rs_;
     const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
     for (int i = 0; i < 2; i++) { adj_[i] = alloc(bytes_, dev); fill_zero(adj_[i]); }
+    // tape budget on the device: TCLB_TAPE_DEVICE_BYTES, else 70 % of what is free now (a B200 has 180 GB); frames
+    // beyond it go to page-locked host memory
     const char *cap = getenv("TCLB_TAPE_DEVICE_BYTES");
-    dev_tape_cap_ = cap ? (size_t)atoll(cap) : ((size_t)8 << 30);
+    if (cap) dev_tape_cap_ = (size_t)atoll(cap);
+    else if (dev) { size_t fr = 0, tot = 0; ADJ_CUDA(cudaMemGetInfo(&fr, &tot)); dev_tape_cap_ = (size_t)(0.7 * (double)fr); }
+    else dev_tape_cap_ = 0;
 }
 Adjoint::~Adjoint() {
     drop_tape();
+    for (void *p : pool_dev_) release(p, true);
+    for (void *p : pool_host_) release(p, false);
     const bool dev = lat_ && lat_->backend == TCLB_BACKEND_CUDA;
     for (int i = 0; i < 2; i++) if (adj_[i]) release(adj_[i], dev);
     if (sg_dev_) cudaFree(sg_dev_);
@@ -60,20 +66,31 @@ Adjoint::~Adjoint() {
 }
 void *Adjoint::alloc(size_t bytes, bool device) const {
     void *p = nullptr;
+    const bool cuda = lat_->backend == TCLB_BACKEND_CUDA;
     if (device) { ADJ_CUDA(cudaSetDevice(lat_->device)); ADJ_CUDA(cudaMalloc(&p, bytes)); }
+    else if (cuda) ADJ_CUDA(cudaMallocHost(&p, bytes));     // page-locked: the tape copies run at full PCIe/C2C rate
     else { p = malloc(bytes); if (!p) fail("adjoint: out of host memory (%zu bytes)", bytes); }
     return p;
 }
 void Adjoint::release(void *p, bool device) const {
-    if (device) cudaFree(p); else free(p);
+    if (device) cudaFree(p);
+    else if (lat_->backend == TCLB_BACKEND_CUDA) cudaFreeHost(p);
+    else free(p);
 }
+// tape frames are recycled: a reverse sweep hands its frames to the next record() instead of freeing them
+void *Adjoint::frame_get(bool device) {
+    std::vector<void *> &pool = device ? pool_dev_ : pool_host_;
+    if (!pool.empty()) { void *p = pool.back(); pool.pop_back(); return p; }
+    return alloc(lat_->snap_bytes, device);
+}
+void Adjoint::frame_put(void *p, bool device) { (device ? pool_dev_ : pool_host_).push_back(p); }
 void Adjoint::fill_zero(void *p) const {
     if (lat_->backend == TCLB_BACKEND_CUDA) ADJ_CUDA(cudaMemsetAsync(p, 0, bytes_, (cudaStream_t)lat_->stream));
     else memset(p, 0, bytes_);
 }
 void Adjoint::zero() { fill_zero(adj_[0]); fill_zero(adj_[1]); }
 void Adjoint::drop_tape() {
-    for (Frame &f : tape_) release(f.data, f.on_device);
+    for (Frame &f : tape_) frame_put(f.data, f.on_device);
     tape_.clear();
     dev_tape_bytes_ = 0;
 }
@@ -84,7 +101,7 @@ void Adjoint::record(int n) {
         Frame f;
         f.iter = lat_->iter;
         f.on_device = dev && dev_tape_bytes_ + lat_->snap_bytes <= dev_tape_cap_;
-        f.data = alloc(lat_->snap_bytes, f.on_device);
+        f.data = frame_get(f.on_device);
         const void *src = lat_->snap_ptr(lat_->cur);
         if (dev) {
             ADJ_CUDA(cudaMemcpyAsync(f.data, src, lat_->snap_bytes, f.on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost,
@@ -130,11 +147,11 @@ void Adjoint::reverse() {
             ADJ_CUDA(cudaMemcpyAsync(stage_buf, f.data, lat_->snap_bytes, cudaMemcpyHostToDevice, (cudaStream_t)lat_->stream));
             src = stage_buf;
         }
-        step(src, f.iter);
-        if (dev) ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
-        release(f.data, f.on_device);
+        step(src, f.iter);      // everything is ordered on the lattice's stream: no host synchronisation per step
+        frame_put(f.data, f.on_device);
         if (f.on_device) dev_tape_bytes_ -= lat_->snap_bytes;
     }
+    if (dev) ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
     if (stage_buf) release(stage_buf, true);
 }
 void Adjoint::steady(int n) {

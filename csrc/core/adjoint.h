@@ -57,6 +57,9 @@ class Adjoint {
     std::vector<Frame> tape_;
     size_t dev_tape_bytes_ = 0, dev_tape_cap_ = 0;
     void step(const void *primal_in, int iter);   // adj_[cur^1] = J^T adj_[cur] + dObj; then swap
+    std::vector<void *> pool_dev_, pool_host_;    // recycled tape frames
+    void *frame_get(bool device);
+    void frame_put(void *p, bool device);
     void *alloc(size_t bytes, bool device) const;
     void release(void *p, bool device) const;
     void fill_zero(void *p) const;

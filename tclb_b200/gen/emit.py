@@ -572,6 +572,7 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     A("#ifdef TCLB_AD")
     ad_mark = len(L)
     A("TCLB_HD void ad_add(base_t *p, base_t v);")
+    A("TCLB_HD void ad_put(base_t *p, base_t v) { if (v != (base_t)0) *p = v; }")
     loaded = [[(di, d) for di, d in enumerate(m.densities) if d.load.get(s.name)] for s in m.stages]
     A("TCLB_HD int ad_inputs_of_stage(int s) {\n    switch (s) {")
     for si in range(len(m.stages)):
@@ -589,8 +590,14 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
                 A(f"    g += n.{f.name} * adj_out[{fidx[f.name]} * a.fstride + n.n_idx];")
         A("    return g;\n}")
         A(f"TCLB_HD void ad_scatter_stage_{si}(const KArgs &a, base_t *adj_in, int x, int i0, int im, int ip, int c, const real_t &g) {{")
+        readers = {}
+        for _, d in loaded[si]:
+            readers[d.field] = readers.get(d.field, 0) + 1
         for k, (di, d) in enumerate(loaded[si]):
-            A(f"    if (c == {k} / TCLB_AD_DIRS) ad_add(adj_in + (a.ldp[{di}] - a.in) + ({_xidx(d.dx)}), g.d[{k} % TCLB_AD_DIRS]);")
+            # a field pulled by ONE density has one reader per cell (the node at cell + c): a plain store into the
+            # zero-filled buffer; several densities on one field (stencil reads) need the atomic
+            put = "ad_put" if readers[d.field] == 1 else "ad_add"
+            A(f"    if (c == {k} / TCLB_AD_DIRS) {put}(adj_in + (a.ldp[{di}] - a.in) + ({_xidx(d.dx)}), g.d[{k} % TCLB_AD_DIRS]);")
         A("}")
     A("template <int S, int GMODE> TCLB_HD void ad_seed_stage(Node<GMODE> &n, int c) {")
     for si in range(len(m.stages)):
