@@ -8,23 +8,25 @@
 #include <cstdio>
 
 namespace {
+// one thread per ghost cell: blockIdx.y enumerates the ghost rows (the 2*gz whole z-planes first, then the 2*gy rows
+// of every interior plane), blockIdx.z the field; interior cells are never visited
 template <class T>
-__global__ void k_fold_ghosts(T *adj, int nfields, int nx, int ny, int nz, int gy, int gz) {
+__global__ void k_fold_ghosts(T *adj, int nx, int ny, int nz, int gy, int gz) {
     const int NY = ny + 2 * gy, NZ = nz + 2 * gz;
-    const long long plane = (long long)nx * NY * NZ;
-    const long long n = (long long)nfields * plane;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const long long r = i % plane;
-        const int x = (int)(r % nx);
-        const int Y = (int)((r / nx) % NY), Z = (int)(r / ((long long)nx * NY));
-        const int y = Y - gy, z = Z - gz;
-        if (y >= 0 && y < ny && z >= 0 && z < nz) continue;
-        const T v = adj[i];
-        if (v == (T)0) continue;
-        const int yy = ((y % ny) + ny) % ny, zz = ((z % nz) + nz) % nz;
-        atomicAdd(&adj[(i - r) + ((long long)(zz + gz) * NY + (yy + gy)) * nx + x], v);
-        adj[i] = (T)0;
-    }
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= nx) return;
+    int r = blockIdx.y, Y, Z;
+    const int nzg = 2 * gz * NY;
+    if (r < nzg) { const int zi = r / NY; Y = r - zi * NY; Z = zi < gz ? zi : zi + nz; }
+    else { r -= nzg; const int zi = r / (2 * gy), k = r - zi * 2 * gy; Z = gz + zi; Y = k < gy ? k : k + ny; }
+    T *base = adj + (size_t)blockIdx.z * ((size_t)nx * NY * NZ);
+    T *src = base + ((size_t)Z * NY + Y) * nx + x;
+    const T v = *src;
+    if (v == (T)0) return;
+    const int y = Y - gy, z = Z - gz;
+    const int yy = ((y % ny) + ny) % ny, zz = ((z % nz) + nz) % nz;
+    atomicAdd(base + ((size_t)(zz + gz) * NY + (yy + gy)) * nx + x, v);
+    *src = (T)0;
 }
 template <class T>
 void fold_host(T *adj, int nfields, int nx, int ny, int nz, int gy, int gz) {
@@ -51,8 +53,12 @@ extern "C" int tclb_adjoint_fold_ghosts(void *adj, int real_size, int on_device,
         else fold_host((float *)adj, nfields, nx, ny, nz, gy, gz);
         return 0;
     }
-    const int tb = 256, nb = 148 * 8;
-    if (real_size == 8) k_fold_ghosts<double><<<nb, tb, 0, (cudaStream_t)stream>>>((double *)adj, nfields, nx, ny, nz, gy, gz);
-    else k_fold_ghosts<float><<<nb, tb, 0, (cudaStream_t)stream>>>((float *)adj, nfields, nx, ny, nz, gy, gz);
+    const int NY = ny + 2 * gy;
+    const int rows = 2 * gz * NY + nz * 2 * gy;
+    const int tb = nx >= 128 ? 128 : 32;
+    dim3 grid((nx + tb - 1) / tb, rows, nfields);
+    if (rows > 65535 || nfields > 65535) return -1;
+    if (real_size == 8) k_fold_ghosts<double><<<grid, tb, 0, (cudaStream_t)stream>>>((double *)adj, nx, ny, nz, gy, gz);
+    else k_fold_ghosts<float><<<grid, tb, 0, (cudaStream_t)stream>>>((float *)adj, nx, ny, nz, gy, gz);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
