@@ -183,7 +183,7 @@ def build_model_lib(variant: str, precision: str = "float", force: bool = False,
 _CUSTOM_MODELS: dict = {}      # library name -> how to load its ModelDef again (models built from a directory)
 
 
-def build_adjoint_lib(variant: str, precision: str = "double", dirs: int = 4, force: bool = False) -> Path:
+def build_adjoint_lib(variant: str, precision: str = "double", dirs: Optional[int] = None, force: bool = False) -> Path:
     """The adjoint companion of a model library: the same generated source compiled with -DTCLB_AD (node code in dual
     numbers, csrc/kernels/tclb_dual.h), exporting ``tclb_model_adjoint_stage``.  The runtime loads
     ``libtclb_<variant>_<precision>_ad.so`` next to the primal library when an adjoint is asked for.  `variant` is a
@@ -201,6 +201,11 @@ def build_adjoint_lib(variant: str, precision: str = "double", dirs: int = 4, fo
             from .models import build_model
             m = build_model(variant)
         text = emit_model_source(m, variant, adjoint=True)
+        if dirs is None:
+            # tangent directions per pass: every input at once for small velocity sets, 5 otherwise (measured on B200:
+            # d2q9 13.5 GLUPS at 9 vs 10.2 at 4; d3q19 spills beyond 7) - profiles/README.md
+            n_in = max((sum(1 for d in m.densities if d.load.get(s.name)) for s in m.stages), default=1)
+            dirs = n_in if n_in <= 9 else 5
         if not src.exists() or src.read_text() != text:
             src.write_text(text)
     target = LIBDIR / f"libtclb_{variant}_{precision}_ad.so"

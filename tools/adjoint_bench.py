@@ -14,6 +14,9 @@ model = sys.argv[1] if len(sys.argv) > 1 else "d2q9"
 prec = sys.argv[2] if len(sys.argv) > 2 else "float"
 nx, ny, nz = (int(v) for v in (sys.argv[3:6] if len(sys.argv) > 5 else (2048, 2048, 1)))
 n = int(sys.argv[6]) if len(sys.argv) > 6 else 20
+import os  # noqa: E402
+if os.environ.get("AD_DIRS"):          # experiment: rebuild the adjoint companion with another chunk width first
+    build.build_adjoint_lib(model, prec, dirs=int(os.environ["AD_DIRS"]))
 import torch  # noqa: E402
 backend = "cuda" if torch.cuda.is_available() else "cpu"
 m = Model(model, prec)
@@ -30,6 +33,7 @@ d.iterate(10)
 d.sync()
 t0 = time.perf_counter(); d.iterate(n); d.sync(); tp = time.perf_counter() - t0
 adj = Adjoint(d)
+adj.record(n); adj.reverse(); adj.zero(); d.sync()          # warm-up: allocates the tape frames (recycled afterwards)
 t0 = time.perf_counter(); adj.record(n); d.sync(); tr = time.perf_counter() - t0
 t0 = time.perf_counter(); adj.reverse(); d.sync(); ta = time.perf_counter() - t0
 nodes = nx * ny * nz * n
