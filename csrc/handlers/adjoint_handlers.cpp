@@ -370,5 +370,92 @@ class AcOptimize : public GenericAction {
 };
 TCLB_REGISTER_HANDLER("Optimize", AcOptimize)
 
+// <Andersen Directions="m" [Times="k"] [Eps="e"]> children </Andersen>: Anderson mixing of the fixed-point iteration
+// "state -> children(state)" (reference src/Handlers/acAndersen.cpp).  The last m residuals r_i = children(x_i) - x_i are
+// kept orthonormal (Gram-Schmidt carries the states x_i and the sum-of-weights p_i along); the next state is the
+// combination with the smallest residual norm whose original weights sum to one: x = sum_i x_i p_i / sum_i p_i^2.
+class AcAndersen : public GenericAction {
+    struct Entry { std::vector<double> x, r; double p; };
+    void get_state(std::vector<double> &v) {
+        v.clear();
+        const int nf = solver->model->d->n_fields;
+        for (int rk : solver->domain->local) {
+            Lattice *l = solver->domain->lat[rk];
+            const size_t n = n_nodes(l);
+            for (int f = 0; f < nf; f++) {
+                const size_t o = v.size();
+                v.resize(o + n);
+                if (solver->model->real_size() == 8) l->copy_field_out(f, v.data() + o);
+                else { std::vector<float> t(n); l->copy_field_out(f, t.data()); for (size_t i = 0; i < n; i++) v[o + i] = t[i]; }
+            }
+        }
+    }
+    void set_state(const std::vector<double> &v) {
+        const int nf = solver->model->d->n_fields;
+        size_t o = 0;
+        for (int rk : solver->domain->local) {
+            Lattice *l = solver->domain->lat[rk];
+            const size_t n = n_nodes(l);
+            for (int f = 0; f < nf; f++, o += n) {
+                if (solver->model->real_size() == 8) l->copy_field_in(f, v.data() + o);
+                else { std::vector<float> t(v.begin() + o, v.begin() + o + n); l->copy_field_in(f, t.data()); }
+            }
+        }
+        if ((int)solver->domain->local.size() == solver->domain->dec.nranks)
+            solver->domain->copy_exchange(solver->domain->lat[solver->domain->local[0]]->cur);
+    }
+    double dot(const std::vector<double> &a, const std::vector<double> &b) {
+        double s = 0;
+        for (size_t i = 0; i < a.size(); i++) s += a[i] * b[i];
+        if (solver->domain->reduce_hook) solver->domain->reduce_hook(&s, 1, TCLB_OP_SUM);
+        return s;
+    }
+  public:
+    int init() override {
+        GenericAction::init();
+        if (!node->has_attr("Directions")) { logf(L_ERROR, "no Directions parameter in %s", node->name.c_str()); return -1; }
+        const int directions = std::max(1, atoi(node->attr("Directions").c_str()));
+        const int times = node->has_attr("Times") ? atoi(node->attr("Times").c_str()) : directions;
+        const double eps = node->has_attr("Eps") ? atof(node->attr("Eps").c_str()) : 0.0;
+        std::vector<Entry> hist;
+        for (int it = 0; it < times; it++) {
+            Entry e;
+            get_state(e.x);
+            if (it == 0) logf(L_OUTPUT, "Size of vector in Andersen: %zu", e.x.size());
+            if (execute_internal()) return -1;
+            unstack();
+            get_state(e.r);
+            for (size_t i = 0; i < e.r.size(); i++) e.r[i] -= e.x[i];
+            const double res = dot(e.r, e.r);
+            logf(L_OUTPUT, "Residual in Andersen: %lg", res);
+            if (!std::isfinite(res) || res < eps || res == 0.0) break;
+            e.p = 1.0;
+            for (const Entry &o : hist) {                 // the stored residuals are orthonormal
+                const double a = dot(e.r, o.r);
+                for (size_t i = 0; i < e.r.size(); i++) { e.r[i] -= a * o.r[i]; e.x[i] -= a * o.x[i]; }
+                e.p -= a * o.p;
+            }
+            const double nrm = std::sqrt(dot(e.r, e.r));
+            if (!(nrm > 0)) break;
+            for (size_t i = 0; i < e.r.size(); i++) { e.r[i] /= nrm; e.x[i] /= nrm; }
+            e.p /= nrm;
+            hist.insert(hist.begin(), std::move(e));
+            if ((int)hist.size() > directions) hist.pop_back();
+            double psum = 0;
+            for (const Entry &o : hist) psum += o.p * o.p;
+            std::vector<double> nx(hist[0].x.size(), 0.0);
+            for (const Entry &o : hist) {
+                const double c = o.p / psum;
+                for (size_t i = 0; i < nx.size(); i++) nx[i] += c * o.x[i];
+            }
+            set_state(nx);
+            if (execute_internal()) return -1;
+            unstack();
+        }
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("Andersen", AcAndersen)
+
 }  // namespace
 }  // namespace tclb
