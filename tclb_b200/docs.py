@@ -50,6 +50,14 @@ ELEMENTS = {
     "Control": ("action", "Iterations", "time-dependent zonal settings from <CSV file Time> + <Param value=expr>"),
     "SyntheticTurbulence": ("action", "Modes Spread Spectrum *WaveLength *WaveNumber *WaveFrequency", "random Fourier modes for turbulent inlets"),
     "RunPython": ("callback", "Iterations file", "Python code with the Solver object (python -m tclb_b200.run)"),
+    "Adjoint": ("container", "type Iterations", "type=unsteady: children run with every iteration on the tape, then the reverse sweep; type=steady: Iterations adjoint iterations around the state the children left"),
+    "Objective": ("action", "<Global>=weight ...", "weights of SUM Globals in the objective (sets the <Global>InObj zonal settings)"),
+    "FDTest": ("container", "Samples Epsilon", "adjoint gradient against central differences for a few design variables (children re-run from the same state)"),
+    "OptSolve": ("action", "Iterations Descent direction", "one-shot optimisation: primal iteration + adjoint iteration + descent step of the parameter fields"),
+    "Optimize": ("container", "MaxEvaluations method Step", "maximises the objective accumulated by the children over the parameter fields (built-in projected gradient method)"),
+    "Threshold": ("container", "Levels", "runs the children on thresholded copies of the design, level i/Levels"),
+    "ThresholdNow": ("action", "Level", "thresholds the parameter fields to 0/1"),
+    "Andersen": ("container", "Directions Times Eps", "Anderson mixing of the fixed-point iteration state -> children(state)"),
     "RunR": ("callback", "Iterations file", "recognised; R is not available, rewrite as RunPython"),
     "Catalyst": ("callback", "", "recognised; unavailable on this box"),
     "Run": ("marker", "", "ignored"),
