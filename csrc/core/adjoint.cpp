@@ -27,6 +27,17 @@ Adjoint::Adjoint(Domain *dom) : dom_(dom), lat_(nullptr) {
     stage_ = a.stages[0];
     for (int f = 0; f < m->d->n_fields; f++)
         if (!m->d->stages[stage_].save_field[f]) fail("adjoint: stage %s does not save field %s", m->d->stages[stage_].name, m->d->fields[f].name);
+    // fields that the node code reads through a stencil accessor (phi(1,0) ...) have more cells in their declared reach
+    // than densities pulling from them; those reads are constants for this adjoint: say so instead of being silently wrong
+    for (int f = 0; f < m->d->n_fields; f++) {
+        const tclb_field_t &F = m->d->fields[f];
+        const long cells = (long)(F.maxx - F.minx + 1) * (F.maxy - F.miny + 1) * (F.maxz - F.minz + 1);
+        long pulls = 0;
+        for (int k = 0; k < m->d->n_densities; k++) if (m->d->densities[k].field_index == f) pulls++;
+        if (cells > std::max(1L, pulls))
+            logf(L_WARNING, "adjoint: field %s is read through a stencil accessor (%ld cells, %ld densities); those reads are treated "
+                            "as constants, gradients through them are missing", F.name, cells, pulls);
+    }
     // companion library: <primal>.so -> <primal>_ad.so
     std::string p = m->path;
     const size_t dot = p.rfind(".so");

@@ -30,7 +30,7 @@ for d, _, files in sorted(os.walk(os.path.join(root, "models"))):
     try:
         m = rfrontend.load_model(d, options=OPTS.get(name))
         src = out / f"try_{name}.cu"
-        src.write_text(emit_model_source(m, "try_" + name))
+        src.write_text(emit_model_source(m, "try_" + name, adjoint=AD))
         jobs.append((name, src))
     except Exception as e:
         status[name] = f"lowering FAILED: {type(e).__name__}: {str(e)[:140]}"
