@@ -88,6 +88,24 @@ TCLB_DUAL_T Dual<T, N> cos(const Dual<T, N> &a) { return tclb_dual_chain(a, (T)s
 TCLB_DUAL_T Dual<T, N> tan(const Dual<T, N> &a) { const T t = std::tan(a.v); return tclb_dual_chain(a, t, (T)1 + t * t); }
 TCLB_DUAL_T Dual<T, N> tanh(const Dual<T, N> &a) { const T t = std::tanh(a.v); return tclb_dual_chain(a, t, (T)1 - t * t); }
 TCLB_DUAL_T Dual<T, N> atan(const Dual<T, N> &a) { return tclb_dual_chain(a, (T)std::atan(a.v), (T)1 / ((T)1 + a.v * a.v)); }
+TCLB_DUAL_T Dual<T, N> sinh(const Dual<T, N> &a) { return tclb_dual_chain(a, (T)std::sinh(a.v), (T)std::cosh(a.v)); }
+TCLB_DUAL_T Dual<T, N> cosh(const Dual<T, N> &a) { return tclb_dual_chain(a, (T)std::cosh(a.v), (T)std::sinh(a.v)); }
+TCLB_DUAL_T Dual<T, N> asin(const Dual<T, N> &a) { return tclb_dual_chain(a, (T)std::asin(a.v), (T)1 / std::sqrt((T)1 - a.v * a.v)); }
+TCLB_DUAL_T Dual<T, N> acos(const Dual<T, N> &a) { return tclb_dual_chain(a, (T)std::acos(a.v), (T)-1 / std::sqrt((T)1 - a.v * a.v)); }
+TCLB_DUAL_T Dual<T, N> cbrt(const Dual<T, N> &a) { const T c = std::cbrt(a.v); return tclb_dual_chain(a, c, c != 0 ? (T)1 / ((T)3 * c * c) : (T)0); }
+TCLB_DUAL_T Dual<T, N> log10(const Dual<T, N> &a) { return tclb_dual_chain(a, (T)std::log10(a.v), (T)0.4342944819032518 / a.v); }
+TCLB_DUAL_T Dual<T, N> log2(const Dual<T, N> &a) { return tclb_dual_chain(a, (T)std::log2(a.v), (T)1.4426950408889634 / a.v); }
+TCLB_DUAL_T Dual<T, N> erf(const Dual<T, N> &a) { return tclb_dual_chain(a, (T)std::erf(a.v), (T)1.1283791670955126 * (T)std::exp(-a.v * a.v)); }
+TCLB_DUAL_T Dual<T, N> atan2(const Dual<T, N> &y, const Dual<T, N> &x) {
+    Dual<T, N> r; r.v = std::atan2(y.v, x.v);
+    const T q = x.v * x.v + y.v * y.v, iq = q > 0 ? (T)1 / q : (T)0;
+    for (int i = 0; i < N; i++) r.d[i] = (x.v * y.d[i] - y.v * x.d[i]) * iq;
+    return r;
+}
+template <class T, int N, class U, class = typename std::enable_if<std::is_arithmetic<U>::value>::type>
+TCLB_HD Dual<T, N> atan2(const Dual<T, N> &y, U x) { return atan2(y, Dual<T, N>((T)x)); }
+template <class T, int N, class U, class = typename std::enable_if<std::is_arithmetic<U>::value>::type>
+TCLB_HD Dual<T, N> atan2(U y, const Dual<T, N> &x) { return atan2(Dual<T, N>((T)y), x); }
 TCLB_DUAL_T Dual<T, N> fabs(const Dual<T, N> &a) { return a.v < 0 ? -a : a; }
 TCLB_DUAL_T Dual<T, N> abs(const Dual<T, N> &a) { return a.v < 0 ? -a : a; }
 TCLB_DUAL_T Dual<T, N> floor(const Dual<T, N> &a) { return Dual<T, N>((T)std::floor(a.v)); }
