@@ -217,8 +217,15 @@ def emit_model_source(m: ModelDef, libname: str, adjoint: bool = False) -> str:
     A("typedef tclb_vec3<real_t> vector_t;")
     # Color() of a model assigns real_t expressions to a float2; the adjoint build never calls it, so there the
     # members just swallow what they are given
-    A("#ifdef TCLB_AD\nstruct tclb_ad_sink { template <class U> TCLB_HD tclb_ad_sink &operator=(const U &) { return *this; } };\n"
-      "struct tclb_ad_float2 { tclb_ad_sink x, y; };\n#define float2 tclb_ad_float2\n#endif")
+    if adjoint:
+        A("#ifdef TCLB_AD\nstruct tclb_ad_sink {\n"
+          "    template <class U> TCLB_HD tclb_ad_sink &operator=(const U &) { return *this; }\n"
+          "    template <class U> TCLB_HD tclb_ad_sink &operator+=(const U &) { return *this; }\n"
+          "    template <class U> TCLB_HD tclb_ad_sink &operator-=(const U &) { return *this; }\n"
+          "    template <class U> TCLB_HD tclb_ad_sink &operator*=(const U &) { return *this; }\n"
+          "    template <class U> TCLB_HD tclb_ad_sink &operator/=(const U &) { return *this; }\n"
+          "    TCLB_HD operator float() const { return 0.f; }\n};\n"
+          "struct tclb_ad_float2 { tclb_ad_sink x, y; };\n#define float2 tclb_ad_float2\n#endif")
     # storage type of the lattice (reference ./configure --with-storage=half|half-shift|float|float-shift|double,
     # src/LatticeAccess.inc.cpp.Rt:14-35): what lives in HBM may be narrower than what the node code computes in, and a
     # per-field constant (AddDensity(shift=)) may be subtracted before storing so that small deviations keep their bits
