@@ -485,7 +485,9 @@ void Lattice::launch_stage(int stage, int in_snap, int out_snap, int gmode, bool
         if (d == 4) continue;
         L.halo_snap[d] = halo[d].snap[out_snap];
         L.halo_ny[d] = halo[d].ny; L.halo_nz[d] = halo[d].nz;
-        if (L.sig_enable && halo[d].rank != rank && halo[d].rank >= 0) {
+        // flags only towards neighbours whose kernels can overlap mine (another device or process); a neighbour on
+        // this device shares my stream, never signals, and must not be waited for
+        if (L.sig_enable && halo[d].concurrent) {
             L.sig_remote[d] = halo[d].flag;
             L.sig_wait[d] = sig_ + d;
         }
@@ -738,7 +740,8 @@ void Domain::finalize_wiring() {
             // sequence flags are only needed between kernels that may run concurrently (different devices or
             // processes); ranks sharing one stream-ordered device do not need them, and the CPU oracle runs
             // ranks one after another.
-            if (backend == TCLB_BACKEND_CUDA && nb != r && (!lat[nb] || lat[nb]->device != L->device)) concurrent = true;
+            t.concurrent = backend == TCLB_BACKEND_CUDA && nb != r && (!lat[nb] || lat[nb]->device != L->device);
+            if (t.concurrent) concurrent = true;
         }
         L->sig_enable = concurrent && all_wired;
         L->halo_mode = (use_direct_halo && all_wired) ? TCLB_HALO_DIRECT : TCLB_HALO_NONE;

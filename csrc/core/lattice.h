@@ -48,6 +48,8 @@ struct HaloTarget {
     void *snap[2] = {nullptr, nullptr};
     int ny = 0, nz = 0;            // interior extent of the owner
     unsigned *flag = nullptr;      // owner's flag word that I publish into (its flags_in[opposite(d)])
+    bool concurrent = false;       // owner runs on another device or in another process: its kernels are not ordered
+                                   // with mine by a stream, so the halo needs the sequence flags
 };
 
 class Lattice {

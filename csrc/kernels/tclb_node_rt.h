@@ -82,6 +82,51 @@ TCLB_D unsigned ld_acquire_sys(const unsigned *p) {
 TCLB_D void st_release_sys(unsigned *p, unsigned v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+TCLB_D unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#ifndef TCLB_HALO_TIMEOUT_NS
+#define TCLB_HALO_TIMEOUT_NS 20000000000ull      // 20 s without a neighbour's halo flag = the peer is gone
+#endif
+
+// ---- bulk asynchronous copies into shared memory (TMA engine, SASS UBLKCP) + mbarrier completion ----
+// Used by the persistent stage kernel: one elected thread streams the rows of the next tile into a
+// shared-memory ring while the block computes the current one.  All sources are this GPU's own snapshot.
+TCLB_D unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+TCLB_D void mbar_init(void *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+TCLB_D void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+TCLB_D void mbar_arrive_expect_tx(void *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+TCLB_D void mbar_wait(void *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "TCLB_MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra TCLB_MBAR_DONE;\n"
+        "bra TCLB_MBAR_WAIT;\n"
+        "TCLB_MBAR_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (size and both addresses multiples of 16 bytes); completion is counted on `bar`
+TCLB_D void bulk_g2s(void *dst, const void *src, unsigned bytes, void *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// one element (4 or 8 bytes) global -> shared without a register in between (LDGSTS)
+template <int BYTES> TCLB_D void cp_async_elem(void *dst, const void *src) {
+    if constexpr (BYTES == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+    else if constexpr (BYTES == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+// this thread's earlier cp.async copies arrive on `bar` when they have landed (the barrier's count includes them)
+TCLB_D void cp_async_arrive_noinc(void *bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 #endif
 
 // piecewise colour map used by the headless raster kernel (values in [0,1])

@@ -27,7 +27,7 @@ CUDA_HOME = Path(os.environ.get("CUDA_HOME", "/usr/local/cuda"))
 NVCC = str(CUDA_HOME / "bin" / "nvcc")
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-fopenmp,-O2",
-              "-Xptxas", "-v", "-diag-suppress", "177,550"]
+              "-Xptxas", "-v", "-diag-suppress", "177,550"] + os.environ.get("TCLB_NVCC_EXTRA", "").split()    # extra -D flags for A/B builds
 CXX_FLAGS = ["-O2", "-g", "-std=c++17", "-fPIC", "-Wall", "-Wno-unused-function", "-fopenmp"]
 
 

@@ -417,13 +417,17 @@ struct Node {
         A(f"    const real_t &{s.name};")
     # brace initialisers: a field of the same name is a function-like macro and would swallow `name(`
     init_refs = "".join(f", {s.name}{{a_.settings[{i}]}}" for i, s in enumerate(m.settings))
-    A("    TCLB_HD Node(const KArgs &a_, int x, int y, int z, real_t *gacc = nullptr) : ka_(a_), n_x(x), n_y(y), n_z(z), gacc_(gacc)" + init_refs + " {")
+    # GMODE bit 8: the accumulators live across the nodes a thread visits (persistent kernel) and are cleared by the
+    # kernel, not per node; `type` >= 0 hands in a node type that was already fetched (shared-memory ring)
+    A("    TCLB_HD Node(const KArgs &a_, int x, int y, int z, real_t *gacc = nullptr, int type = -1) : ka_(a_), n_x(x), n_y(y), n_z(z), gacc_(gacc)" + init_refs + " {")
     A(r"""
         n_idx = ((z + GZ) * ka_.NY + (y + GY)) * ka_.nx + x;
-        n_type = ka_.flags[n_idx];
-        if (GMODE & 1) {
-            for (int i = 0; i < N_GLOBALS; i++) gacc_[i * GSTRIDE] = (i >= SUM_GLOBALS) ? (real_t)-1e30 : (real_t)0;
-        } else if ((GMODE & 3) == 2) gacc_[0] = 0;""")
+        n_type = type >= 0 ? (flag_t)type : ka_.flags[n_idx];
+        if (!(GMODE & 8)) {
+            if (GMODE & 1) {
+                for (int i = 0; i < N_GLOBALS; i++) gacc_[i * GSTRIDE] = (i >= SUM_GLOBALS) ? (real_t)-1e30 : (real_t)0;
+            } else if ((GMODE & 3) == 2) gacc_[0] = 0;
+        }""")
     for i, s in enumerate(m.zonesettings):
         if s.name in member_zs:
             A(f"        {s.name} = zone_setting({i});")
@@ -557,6 +561,77 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
                 A(f"        halo_put<{f.miny},{f.maxy},{f.minz},{f.maxz}>(a, {fi}, x, y, z, TCLB_ST(n.{f.name}, {shift_of[f.name]!r}));")
         A("    }")
         A("}")
+    # ---- persistent kernel with a shared-memory ring fed by bulk asynchronous copies (scaffold.cu.in k_stage_persist) ----
+    # Per stage: every loaded density is one row of the tile (TCLB_TILE_X consecutive x at the pulled y/z), copied by ONE
+    # cp.async.bulk; the |dx| elements a pulled row needs from beyond the tile (periodic in x) come as single-element
+    # cp.async copies, so a row sits in shared memory with 16 bytes of room on either side.
+    A("#if defined(__CUDACC__) && !defined(TCLB_AD)")
+    A("constexpr int TCLB_TILE_X = 128;")
+    A("constexpr int RING_PAD = 16 / (int)sizeof(storage_t) > 0 ? 16 / (int)sizeof(storage_t) : 1;   // elements of room before/after a row")
+    A("constexpr int RING_ROW = (TCLB_TILE_X + 2 * RING_PAD) * (int)sizeof(storage_t);               // bytes per row")
+    ring_ok = []
+    for si, s_ in enumerate(m.stages):
+        ld = [(di, d) for di, d in enumerate(m.densities) if d.load.get(s_.name)]
+        edges = []      # (row, element position relative to the row start, density index)
+        for k, (di, d) in enumerate(ld):
+            if d.dx > 0:
+                edges += [(k, -j, di) for j in range(1, d.dx + 1)]
+            elif d.dx < 0:
+                edges += [(k, 128 + j, di) for j in range(0, -d.dx)]
+        ok = bool(ld) and all(abs(d.dx) <= 2 for _, d in ld)
+        ring_ok.append(ok)
+        A(f"constexpr int RING_ROWS_{si} = {len(ld) if ok else 0}, RING_EDGES_{si} = {len(edges) if ok else 0};")
+        A(f"constexpr int RING_BYTES_{si} = RING_ROWS_{si} * RING_ROW + TCLB_TILE_X * (int)sizeof(flag_t);")
+        A(f"constexpr bool RING_OK_{si} = {'true' if ok else 'false'} && sizeof(storage_t) >= 4;")
+        A(f"template <int GMODE> TCLB_D void load_stage_ring_{si}(Node<GMODE> &n, const unsigned char *sb, int t) {{")
+        if ok:
+            for k, (di, d) in enumerate(ld):
+                A(f"    n.{d.name} = TCLB_LD(((const storage_t *)(sb + {k} * RING_ROW))[RING_PAD + t - ({d.dx})], {shift_of[d.field]!r});")
+            for di, d in enumerate(m.densities):
+                if not d.load.get(s_.name) and d.default is not None:
+                    A(f"    n.{d.name} = (real_t){d.default!r};")
+        A("}")
+        # rows: issued by one thread; `row0` = index of the tile's first node in a field
+        A(f"TCLB_D void ring_issue_rows_{si}(const KArgs &a, unsigned char *sb, void *bar, long long row0) {{")
+        if ok:
+            A(f"    tclbrt::mbar_arrive_expect_tx(bar, (unsigned)(RING_ROWS_{si} * TCLB_TILE_X * (int)sizeof(storage_t) + TCLB_TILE_X * (int)sizeof(flag_t)));")
+            for k, (di, d) in enumerate(ld):
+                A(f"    tclbrt::bulk_g2s(sb + {k} * RING_ROW + 16, a.ldp[{di}] + row0, TCLB_TILE_X * (unsigned)sizeof(storage_t), bar);")
+            A(f"    tclbrt::bulk_g2s(sb + RING_ROWS_{si} * RING_ROW, a.flags + row0, TCLB_TILE_X * (unsigned)sizeof(flag_t), bar);")
+        A("}")
+        # edge elements: spread over the lanes of the issuing warp
+        if ok and edges:
+            # one packed word per edge element in constant memory: row | field << 8 | (position + 8) << 16 | (dy + 2) << 24 |
+            # (dz + 2) << 27 (the source pointer is rebuilt from these: indexing the kernel parameter array with a lane
+            # dependent index would make the compiler copy it to local memory)
+            def _w(e):
+                d_ = m.densities[e[2]]
+                return e[0] | (fidx[d_.field] << 8) | ((e[1] + 8) << 16) | ((d_.dy + 2) << 24) | ((d_.dz + 2) << 27)
+            A(f"__constant__ int t_ring_edges_{si}[{len(edges)}] = {{{', '.join(str(_w(e)) for e in edges)}}};")
+        A(f"TCLB_D void ring_issue_edges_{si}(const KArgs &a, unsigned char *sb, int lane, long long row0, int x0) {{")
+        if ok and edges:
+            A(f"    for (int e = lane; e < {len(edges)}; e += 32) {{")
+            A(f"        const int w = t_ring_edges_{si}[e], row = w & 255, fi = (w >> 8) & 255, p = ((w >> 16) & 255) - 8, dy = ((w >> 24) & 7) - 2, dz = ((w >> 27) & 7) - 2;")
+            A("        int xs = x0 + p; if (xs < 0) xs += a.nx; if (xs >= a.nx) xs -= a.nx;")
+            A("        const storage_t *src = a.in + (long long)fi * a.fstride - ((long long)dz * a.NY + dy) * a.nx + (row0 - x0) + xs;")
+            A("        tclbrt::cp_async_elem<(int)sizeof(storage_t)>(sb + row * RING_ROW + 16 + p * (int)sizeof(storage_t), src);")
+            A("    }")
+        A("}")
+    A("template <int S, int GMODE> TCLB_D void load_stage_ring(Node<GMODE> &n, const unsigned char *sb, int t) {")
+    for si in range(len(m.stages)):
+        A(f"    if (S == {si}) load_stage_ring_{si}(n, sb, t);")
+    A("}")
+    A("template <int S> TCLB_D void ring_issue_rows(const KArgs &a, unsigned char *sb, void *bar, long long row0) {")
+    for si in range(len(m.stages)):
+        A(f"    if (S == {si}) ring_issue_rows_{si}(a, sb, bar, row0);")
+    A("}")
+    A("template <int S> TCLB_D void ring_issue_edges(const KArgs &a, unsigned char *sb, int lane, long long row0, int x0) {")
+    for si in range(len(m.stages)):
+        A(f"    if (S == {si}) ring_issue_edges_{si}(a, sb, lane, row0, x0);")
+    A("}")
+    A("template <int S> constexpr bool ring_ok() { return " + " || ".join(f"(S == {si} && RING_OK_{si})" for si in range(len(m.stages))) + "; }")
+    A("template <int S> constexpr int ring_bytes() { return " + " + ".join(f"(S == {si} ? RING_BYTES_{si} : 0)" for si in range(len(m.stages))) + "; }")
+    A("#endif")
     A("template <int GMODE> TCLB_HD void load_all(Node<GMODE> &n, const KArgs &a, int x, int i0, int im, int ip) {")
     for di, d in enumerate(m.densities):
         A(f"    n.{d.name} = TCLB_LD(a.ldp[{di}][{_xidx(d.dx)}], {shift_of[d.field]!r});")

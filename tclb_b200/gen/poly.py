@@ -238,11 +238,20 @@ def _mono_c(m: Mono) -> Tuple[str, str]:
     return "*".join(num), "*".join(den)
 
 
-def to_c(p: "Poly | Number | str") -> str:
-    """C expression text (double literals; the float build rewrites literals later)."""
+def _fmt_int(c: Number) -> str:
+    f = float(c)
+    return str(int(round(f))) if abs(f - round(f)) < 1e-12 else _fmt_num(c)
+
+
+def to_c(p: "Poly | Number | str", floating: bool = True, wrap_const=None) -> str:
+    """C expression text (double literals; the float build rewrites literals later).  `floating=False` prints whole
+    numbers as integers (index arithmetic); `wrap_const(text) -> text` wraps every numeric constant (polyAlgebra's
+    C(..., float=FALSE, wrap.const=f))."""
     p = Poly.lift(p)
+    fmt = _fmt_num if floating else _fmt_int
     if p.is_zero():
-        return "0.0"
+        z = fmt(0)
+        return wrap_const(z) if wrap_const else z
     parts: List[str] = []
     for m, c in sorted(p.t.items(), key=lambda kv: (len(kv[0]), kv[0])):
         num, den = _mono_c(m)
@@ -250,9 +259,15 @@ def to_c(p: "Poly | Number | str") -> str:
         ac = -c if neg else c
         one = (ac == 1) if isinstance(ac, (int, Fraction)) else abs(ac - 1.0) < 1e-15
         if num:
-            body = num if one else f"{num}*{_fmt_num(ac)}"
+            body = num if one else f"{num}*{wrap_const(fmt(ac)) if wrap_const else fmt(ac)}"
+        elif wrap_const and not den:
+            # a bare constant is wrapped with its sign, so that it stays one object of the wrapper's type
+            body = wrap_const(fmt(c))
+            neg = False if not parts else neg
+            if parts:
+                body = wrap_const(fmt(ac))
         else:
-            body = _fmt_num(ac)
+            body = fmt(ac)
         if den:
             body = f"{body}/({den})" if "*" in den else f"{body}/{den}"
         if not parts:

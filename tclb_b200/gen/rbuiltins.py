@@ -83,8 +83,14 @@ def install(I):
                 parts.append([to_c(p) for p in x])
             elif isinstance(x, Poly):
                 parts.append([to_c(x)])
+            elif isinstance(x, DataFrame):       # a list of columns: each column is one string (as.character of it)
+                parts.append([to_str(c[0]) if len(c) == 1 else "c(" + ", ".join(to_str(v) for v in c) + ")" for c in x.cols.values()])
+            elif isinstance(x, RList):
+                parts.append([to_str(scalar(v)) if not isinstance(v, (RList, DataFrame)) and vec(v).size == 1 else str(v) for v in x.values()])
             else:
                 parts.append([to_str(v) for v in vec(x).ravel().tolist()])
+        if any(len(p) == 0 for p in parts) and collapse is NULL:
+            return np.array([], dtype=object)          # a zero-length argument gives character(0)
         parts = [p for p in parts if len(p) > 0]
         if not parts:
             return vec([""]) if collapse is NULL else vec("")
@@ -191,21 +197,41 @@ def install(I):
     G.set("as.vector", lambda I, a, k: a[0] if isinstance(a[0], PVec) else vec(a[0]).ravel(order="F"))
     G.set("as.matrix", lambda I, a, k: _as_matrix(a[0]))
     G.set("is.null", lambda I, a, k: vec(a[0] is NULL))
-    G.set("is.na", lambda I, a, k: np.array([v is None or (isinstance(v, float) and math.isnan(v)) for v in vec(a[0]).ravel().tolist()], dtype=bool))
-    G.set("is.character", lambda I, a, k: vec(is_str_vec(vec(a[0])) if a[0] is not NULL else False))
-    G.set("is.numeric", lambda I, a, k: vec(is_vec(vec(a[0])) and vec(a[0]).dtype in (np.int64, float)) if not isinstance(a[0], (RList, DataFrame, PVec, Poly)) else vec(False))
-    G.set("is.logical", lambda I, a, k: vec(vec(a[0]).dtype == bool))
+    def _is_na(I, a, k):
+        x = a[0]
+        isna = lambda v: v is None or (isinstance(v, float) and math.isnan(v))
+        if isinstance(x, DataFrame):
+            return np.array([[isna(c[i]) for c in x.cols.values()] for i in range(x.nrow())], dtype=bool).reshape(x.nrow(), x.ncol())
+        if isinstance(x, (RList, PVec, Poly)):
+            return np.zeros(len(x) if not isinstance(x, Poly) else 1, dtype=bool)
+        v = vec(x)
+        return np.array([isna(t) for t in v.ravel().tolist()], dtype=bool).reshape(v.shape)
+    G.set("is.na", _is_na)
+    def _is_chr(x):
+        if x is NULL or isinstance(x, (RList, DataFrame, PVec, Poly)) or not is_vec(vec(x)):
+            return False
+        v = vec(x)
+        return v.dtype == object and any(isinstance(t, str) for t in v.ravel().tolist())
+    def _is_lgl(x):
+        if x is NULL or isinstance(x, (RList, DataFrame, PVec, Poly)) or not is_vec(vec(x)):
+            return False
+        v = vec(x)
+        return v.dtype == bool or (v.dtype == object and v.size > 0 and all(t is None or isinstance(t, (bool, np.bool_)) for t in v.ravel().tolist()))
+    G.set("is.character", lambda I, a, k: vec(_is_chr(a[0])))
+    G.set("is.numeric", lambda I, a, k: vec(is_vec(vec(a[0])) and vec(a[0]).dtype in (np.int64, float)) if not isinstance(a[0], (RList, DataFrame, PVec, Poly))
+          else vec(isinstance(a[0], Poly) and a[0].is_const()))      # a constant polynomial counts as a number (polyAlgebra)
+    G.set("is.logical", lambda I, a, k: vec(_is_lgl(a[0])))
     G.set("is.function", lambda I, a, k: vec(isinstance(a[0], Closure) or callable(a[0])))
     G.set("is.list", lambda I, a, k: vec(isinstance(a[0], (RList, DataFrame))))
     G.set("is.data.frame", lambda I, a, k: vec(isinstance(a[0], DataFrame)))
     G.set("is.matrix", lambda I, a, k: vec(is_vec(vec(a[0])) and vec(a[0]).ndim == 2))
     G.set("inherits", lambda I, a, k: vec(scalar(a[1]) in ("gvector", "pAlg") and isinstance(a[0], (Poly, PVec))))
-    G.set("class", lambda I, a, k: vec("gvector" if isinstance(a[0], (Poly, PVec)) else "list" if isinstance(a[0], RList) else "data.frame" if isinstance(a[0], DataFrame)
+    G.set("class", lambda I, a, k: vec(a[0].rclass) if isinstance(a[0], RList) and getattr(a[0], "rclass", None) else vec("gvector" if isinstance(a[0], (Poly, PVec)) else "list" if isinstance(a[0], RList) else "data.frame" if isinstance(a[0], DataFrame)
                                        else "function" if isinstance(a[0], Closure) else "character" if is_str_vec(vec(a[0])) else "numeric"))
     G.set("identical", lambda I, a, k: vec(_flat([a[0]]) == _flat([a[1]])))
     G.set("any", lambda I, a, k: vec(any(bool(v) for v in _flat(a))))
     G.set("all", lambda I, a, k: vec(all(bool(v) for v in _flat(a))))
-    G.set("which", lambda I, a, k: np.array([i + 1 for i, v in enumerate(vec(a[0]).ravel().tolist()) if v], dtype=np.int64))
+    G.set("which", lambda I, a, k: np.array([i + 1 for i, v in enumerate(vec(a[0]).ravel(order="F").tolist()) if v], dtype=np.int64))
     G.set("which.max", lambda I, a, k: vec(int(np.argmax(_numv(a[0]))) + 1))
     G.set("which.min", lambda I, a, k: vec(int(np.argmin(_numv(a[0]))) + 1))
     G.set("ifelse", lambda I, a, k: _ifelse(a[0], a[1], a[2]))
@@ -255,11 +281,40 @@ def install(I):
     G.set("substr", lambda I, a, k: vec([to_str(v)[int(scalar(a[1])) - 1:int(scalar(a[2]))] for v in vec(a[0]).tolist()]))
     G.set("strsplit", lambda I, a, k: RList.make([vec(re.split(re.escape(scalar(a[1])) if truthy(k.get("fixed", vec(False))) else scalar(a[1]), to_str(v))) for v in vec(a[0]).tolist()]))
     G.set("trimws", lambda I, a, k: vec([to_str(v).strip() for v in vec(a[0]).tolist()]))
-    G.set("format", lambda I, a, k: vec([to_str(v) for v in vec(a[0]).tolist()]))
+    def _format(I, a, k):
+        items = [to_str(v) for v in vec(a[0]).ravel().tolist()]
+        just = scalar(k.get("justify", vec("left")))
+        if "justify" in k or is_str_vec(vec(a[0])):
+            w = max([len(t) for t in items] + [0])
+            items = [t.ljust(w) if just == "left" else t.rjust(w) if just == "right" else t.center(w) for t in items]
+        return vec(items) if items else np.array([], dtype=object)
+    G.set("format", _format)
     G.set("formatC", G.get("format"))
     G.set("file.exists", lambda I, a, k: vec(I.find_file(scalar(a[0])) is not None))
     G.set("readLines", lambda I, a, k: vec(open(I.find_file(scalar(a[0]))).read().split("\n")))
     G.set("Sys.time", lambda I, a, k: vec(0.0))
+
+    # connections: pipe(cmd) + readLines(con) + close(con) (src/conf.R git_version); the command runs in the first
+    # include directory's parent; a failing command reads as no lines
+    def _pipe(I, a, k):
+        r = RList.make([vec(scalar(a[0]))], ["cmd"])
+        r.rclass = ["pipe", "connection"]
+        return r
+    G.set("pipe", _pipe)
+    G.set("close", lambda I, a, k: NULL)
+    _plain_readlines = G.get("readLines")
+
+    def _readlines(I, a, k):
+        if isinstance(a[0], RList) and "pipe" in (getattr(a[0], "rclass", None) or []):
+            import subprocess
+            try:
+                out = subprocess.run(scalar(a[0]["cmd"]), shell=True, capture_output=True, text=True, timeout=20).stdout
+            except Exception:
+                out = ""
+            lines = [l for l in out.split("\n") if l != ""]
+            return vec(lines) if lines else np.array([], dtype=object)
+        return _plain_readlines(I, a, k)
+    G.set("readLines", _readlines)
     G.set("nlevels", lambda I, a, k: vec(0))
     G.set("rows", lambda I, a, k: _rows(a[0]))
     G.set("pi", vec(math.pi))
@@ -302,6 +357,10 @@ def install(I):
         return np.array(out, dtype=bool)
 
     def _names(x):
+        if isinstance(x, Poly):
+            return vec(list(x.symbols()) + [".M"])
+        if isinstance(x, PVec) and len(x) == 1:
+            return vec(list(x[0].symbols()) + [".M"])
         if isinstance(x, RList):
             return vec(x.names())
         if isinstance(x, DataFrame):
@@ -510,6 +569,13 @@ def install(I):
                     kw[nm] = v
                 else:
                     pos.append(v)
+        elif isinstance(args, DataFrame):      # a data frame is a list of its columns
+            from .rinterp import _col_value
+            for nm, col in args.cols.items():
+                if isinstance(fn, Closure) and nm in [p_[0] for p_ in fn.params]:
+                    kw[nm] = _col_value(col)
+                else:
+                    pos.append(_col_value(col))
         return I.call(fn, pos, kw)
 
     @bi("apply")
@@ -653,24 +719,35 @@ def install_poly(I):
     def _C(I, a, k):
         eq = scalar(k.get("eq", vec("=")))
         sep = scalar(k.get("sep", vec(";\n")))
+        floating = truthy(k["float"]) if "float" in k else True
+        wrap = None
+        if "wrap.const" in k and k["wrap.const"] is not NULL:
+            wfn = k["wrap.const"]
+            wrap = lambda text: to_str(scalar(I.call(wfn, [vec(float(text))], OrderedDict())))
+        if not floating or wrap:
+            _base = to_c
+            def to_c_(p_):
+                return _base(p_, floating=floating, wrap_const=wrap)
+        else:
+            to_c_ = to_c
         if len(a) == 1:
             x = a[0]
-            items = [to_c(p) for p in x] if isinstance(x, PVec) else [to_c(x) if isinstance(x, Poly) else to_str(scalar(x))]
+            items = [to_c_(p) for p in x] if isinstance(x, PVec) else [to_c_(x) if isinstance(x, Poly) else to_str(scalar(x))]
             I.out.append((sep if "sep" in k else ", ").join(items) if len(items) > 1 else items[0])
             return NULL
         lhs, rhs = a[0], a[1]
         if (isinstance(lhs, PVec) and isinstance(rhs, PVec) and len(lhs) == len(rhs) >= 2 and not getattr(I, "plain_c", False)
                 and eq in ("=", "+=", "-=") and all(len(p.t) == 1 for p in lhs)):
             # symbolic block: same rewriting as the native models get (one reciprocal per divisor, shared products)
-            I.out.append(c_assign([to_c(p) for p in lhs], list(rhs), op=eq, indent=""))
+            I.out.append(c_assign([to_c_(p) for p in lhs], list(rhs), op=eq, indent=""))
             return NULL
-        L = [to_c(p) for p in lhs] if isinstance(lhs, PVec) else [to_c(lhs)] if isinstance(lhs, Poly) else [to_str(v) for v in vec(lhs).tolist()]
+        L = [to_c_(p) for p in lhs] if isinstance(lhs, PVec) else [to_c_(lhs)] if isinstance(lhs, Poly) else [to_str(v) for v in vec(lhs).tolist()]
         if isinstance(rhs, PVec):
-            R = [to_c(p) for p in rhs]
+            R = [to_c_(p) for p in rhs]
         elif isinstance(rhs, Poly):
-            R = [to_c(rhs)]
+            R = [to_c_(rhs)]
         else:
-            R = [to_c(Poly.const(float(v))) if not isinstance(v, str) else v for v in vec(rhs).ravel(order="F").tolist()]
+            R = [to_c_(Poly.const(float(v))) if not isinstance(v, str) else v for v in vec(rhs).ravel(order="F").tolist()]
         n = max(len(L), len(R))
         I.out.append("".join(f"{L[i % len(L)]} {eq} {R[i % len(R)]};\n" for i in range(n)))
         return NULL
@@ -744,7 +821,30 @@ def install_poly(I):
         return a[0]
     G.set("provideDimnames", _provide_dimnames)
     G.set("as.data.frame", lambda I, a, k: I.call(G.get("data.frame"), [a[0]], OrderedDict()))
-    G.set("deriv", lambda I, a, k: (_ for _ in ()).throw(RError("deriv() of symbolic expressions is not supported by this front-end")))
+    def _deriv_poly(p, var):
+        out = {}
+        for m, c in p.t.items():
+            d = dict(m)
+            e = d.get(var, 0)
+            if e == 0:
+                continue
+            if e == 1:
+                d.pop(var)
+            else:
+                d[var] = e - 1
+            key = tuple(sorted(d.items()))
+            out[key] = out.get(key, 0) + c * e
+        return Poly(out)
+
+    def _deriv(I, a, k):
+        """polyAlgebra deriv(expr, name): partial derivative of a (Laurent) polynomial with respect to one symbol"""
+        x, var = a[0], scalar(a[1])
+        if isinstance(x, PVec):
+            return PVec([_deriv_poly(p_, var) for p_ in x])
+        if isinstance(x, Poly):
+            return _deriv_poly(x, var)
+        return Poly.const(0.0)
+    G.set("deriv", _deriv)
     G.set("c_header", lambda I, a, k: NULL)
     G.set("c_table_decl", lambda I, a, k: a[0])
     G.set("ifdef", lambda I, a, k: NULL)

@@ -334,6 +334,27 @@ class Interp:
                 return NULL
             if fname == "on.exit":
                 return NULL
+            if fname == "switch":
+                sel = scalar(self.eval(args[0][1], env))
+                alts = args[1:]
+                if isinstance(sel, str):
+                    hit = None
+                    for i, (nm, a_) in enumerate(alts):
+                        if nm == sel:
+                            hit = i
+                            break
+                    if hit is None:
+                        for i, (nm, a_) in enumerate(alts):
+                            if nm is None:
+                                hit = i
+                                break
+                    if hit is None:
+                        return NULL
+                    while hit < len(alts) and alts[hit][1][0] == "missing":      # `a=, b=expr`: fall through
+                        hit += 1
+                    return self.eval(alts[hit][1], env) if hit < len(alts) else NULL
+                i = int(sel) - 1
+                return self.eval(alts[i][1], env) if 0 <= i < len(alts) else NULL
             if fname == "stopifnot":
                 for _, a in args:
                     if not truthy(np.all(vec(self.eval(a, env)))):
@@ -381,7 +402,16 @@ class Interp:
         else:
             fn = self.eval(fnode, env)
         pos, kw = self.eval_args(args, env)
-        return self.call(fn, pos, kw)
+        try:
+            return self.call(fn, pos, kw)
+        except (_Break, _Next, _Return):
+            raise
+        except Exception as e:
+            if not hasattr(e, "rstack"):
+                e.rstack = []
+            if len(e.rstack) < 12:
+                e.rstack.append(fnode[1] if fnode[0] == "name" else "<fn>")
+            raise
 
     # ---- source() ----
     def find_file(self, name):
@@ -519,6 +549,14 @@ class Interp:
             return A * B
         if op == "/":
             return A * (B ** -1) if isinstance(B, Poly) else PVec([x * (y ** -1) for x, y in zip(A, B)])
+        if op in ("<", ">", "<=", ">="):
+            la = [x for x in (A if isinstance(A, PVec) else [A])]
+            lb = [x for x in (B if isinstance(B, PVec) else [B])]
+            if not all(x.is_const() for x in la + lb):
+                raise RError(f"operator {op} needs constant symbolic values")
+            f = {"<": lambda p, q: p < q, ">": lambda p, q: p > q, "<=": lambda p, q: p <= q, ">=": lambda p, q: p >= q}[op]
+            n = max(len(la), len(lb))
+            return np.array([f(float(la[i % len(la)].const_value()), float(lb[i % len(lb)].const_value())) for i in range(n)], dtype=bool)
         if op in ("==", "!="):
             from .poly import to_c
             la = [to_c(x) for x in (A if isinstance(A, PVec) else [A])]
@@ -570,14 +608,16 @@ class Interp:
                     k = list(x.cols)[c]
                     d.cols[k] = list(x.cols[k])
                 return d
-            rows = self._pos_index(idxs[0], x.nrow())
+            rows = self._pos_index(idxs[0], x.nrow(), getattr(x, "rownames", None))
             cols = self._pos_index(idxs[1], x.ncol(), list(x.cols))
             keys = [list(x.cols)[c] for c in cols]
             if len(keys) == 1 and drop:
-                return vec([x.cols[keys[0]][r] for r in rows])
+                return _col_value([x.cols[keys[0]][r] for r in rows])
             d = DataFrame()
             for k in keys:
                 d.cols[k] = [x.cols[k][r] for r in rows]
+            if getattr(x, "rownames", None):
+                d.rownames = [x.rownames[r] for r in rows]
             return d
         if isinstance(x, RList):
             keys = list(x.keys())
@@ -646,7 +686,7 @@ class Interp:
                     name = cand[0]
                 else:
                     return NULL
-            return vec(list(x.cols[name]))
+            return _col_value(x.cols[name])
         if isinstance(x, RList):
             if name in x:
                 return x[name]
@@ -695,8 +735,14 @@ class Interp:
         if k == "dollar":
             name = target[2]
             if isinstance(cur, DataFrame):
-                d = DataFrame(OrderedDict((kk, list(v)) for kk, v in cur.cols.items()))
-                v = vec(val).tolist() if not isinstance(val, list) else val
+                d = _df_copy(cur)
+                from .poly import PVec as _PV
+                if isinstance(val, RList):
+                    v = list(val.values())
+                elif isinstance(val, _PV):
+                    v = list(val)
+                else:
+                    v = vec(val).tolist() if not isinstance(val, list) else val
                 n = d.nrow()
                 d.cols[name] = [v[i % len(v)] for i in range(n)] if n else list(v)
                 return d
@@ -733,9 +779,9 @@ class Interp:
                     out[p] = vals[j % len(vals)]
                 return out
             if isinstance(cur, DataFrame):
-                d = DataFrame(OrderedDict((kk, list(v)) for kk, v in cur.cols.items()))
+                d = _df_copy(cur)
                 if len(idxs) == 2:
-                    rows = self._pos_index(idxs[0], d.nrow())
+                    rows = self._pos_index(idxs[0], d.nrow(), getattr(d, "rownames", None))
                     if idxs[1] is not MISSING and is_str_vec(vec(idxs[1])):
                         keys = vec(idxs[1]).tolist()
                         for kk in keys:
@@ -783,6 +829,9 @@ class Interp:
                         a = np.append(a, [None] if a.dtype == object else [0])
                 pos = [names.index(s) for s in vec(idxs[0]).tolist()]
             else:
+                li = vec(idxs[0]) if idxs[0] is not MISSING else None
+                if li is not None and li.dtype == bool and li.size > a.size and a.ndim == 1:
+                    a = np.concatenate([a.astype(object), np.array([None] * (li.size - a.size), dtype=object)]) if True else a
                 pos = self._pos_index(idxs[0], a.size if a.ndim == 1 else a.size)
             if a.ndim == 2:
                 flat = a.ravel(order="F")
@@ -807,11 +856,25 @@ class Interp:
                         d.cols[kk] = list(v)
                     return d
                 return NamedVec(vec(cur), nm)
+            if fname == "class" and isinstance(cur, RList):
+                out = RList(cur)
+                out.rclass = vec(val).tolist()
+                return out
+            if fname in ("rownames", "row.names") and isinstance(cur, DataFrame):
+                d = _df_copy(cur)
+                d.rownames = [to_str(v) for v in vec(val).tolist()] if val is not NULL else None
+                return d
             if fname in ("colnames", "rownames", "row.names", "dimnames", "class", "levels"):
                 if fname == "colnames" and is_vec(vec(cur)) and vec(cur).ndim == 2:
                     return NamedMat(vec(cur), vec(val).tolist())
                 return cur
             if fname == "dim":
+                if val is NULL:
+                    from .poly import PVec as _PV
+                    if isinstance(cur, _PV):
+                        cur.dim = None
+                        return cur
+                    return vec(cur).ravel(order="F") if not isinstance(cur, RList) else cur
                 d = [int(t) for t in vec(val).tolist()]
                 if isinstance(cur, (RList,)):
                     return cur
@@ -831,6 +894,27 @@ class Interp:
                 np.fill_diagonal(a, vec(val))
                 return a
         raise RError("unsupported replacement form")
+
+
+def _df_copy(cur):
+    d = DataFrame(OrderedDict((kk, list(v)) for kk, v in cur.cols.items()))
+    d.rownames = list(cur.rownames) if getattr(cur, "rownames", None) else None
+    return d
+
+
+def _is_cell_scalar(c):
+    return c is None or isinstance(c, (str, int, float, bool, np.generic))
+
+
+def _col_value(col):
+    """a data-frame column as an R value: an atomic vector, or a list when the cells are not scalars (I(list(...)))"""
+    col = list(col)
+    if all(_is_cell_scalar(c) for c in col):
+        return vec(col)
+    from .poly import Poly, PVec
+    if all(isinstance(c, Poly) for c in col):
+        return PVec(col)
+    return RList.make(col)
 
 
 class NamedVec(np.ndarray):

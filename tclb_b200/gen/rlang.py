@@ -76,13 +76,18 @@ class DataFrame:
     def row(self, i) -> RList:
         r = RList()
         for k, v in self.cols.items():
-            r[k] = vec([v[i]])
+            c = v[i]
+            # a cell of a list column (I(list(...)), closures, symbolic values) is handed out as it is
+            r[k] = c if isinstance(c, (np.ndarray, RList, DataFrame)) or callable(c) or hasattr(c, "__rcell__") or (c is not None and not isinstance(c, (str, int, float, bool, np.generic))) else vec([c])
         return r
 
     def subset_rows(self, idx: List[int]) -> "DataFrame":
         d = DataFrame()
         for k, v in self.cols.items():
             d.cols[k] = [v[i] for i in idx]
+        rn = getattr(self, "rownames", None)
+        if rn:
+            d.rownames = [rn[i] for i in idx]
         return d
 
     def rbind(self, other: "DataFrame") -> "DataFrame":

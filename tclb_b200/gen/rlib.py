@@ -59,8 +59,13 @@ def _pvec(x) -> PVec:
 
 
 def _densities(I) -> List[dict]:
-    m = I.globals.model
-    return [d for d in m.density_dicts() if not d.get("adjoint")]
+    m = getattr(I.globals, "model", None)
+    if m is not None:
+        return [d for d in m.density_dicts() if not d.get("adjoint")]
+    # no ModelDef behind the interpreter (the reference's own conf.R was sourced): read its Density table
+    D = I.globals.get("Density")
+    c = D.cols
+    return [dict(name=c["name"][i], dx=int(c["dx"][i]), dy=int(c["dy"][i]), dz=int(c["dz"][i]), group=c["group"][i]) for i in range(D.nrow())]
 
 
 # ---------------------------------------------------------------------------------------------- lattice.R

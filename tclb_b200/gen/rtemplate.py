@@ -18,13 +18,20 @@ from .rlang import NULL, RError, scalar, vec
 _TAG = re.compile(r"<\?(RT\b|R\b|%[-0-9.]*[a-zA-Z]|python\b)?(.*?)\?>", re.S)
 
 
-def template_to_program(text: str, texts: List[str]) -> str:
+class _Lit(str):
+    """literal chunk of a template that remembers where it ends (file, line): error messages point there"""
+    where = ("", 0)
+
+
+def template_to_program(text: str, texts: List[str], path: str = "") -> str:
     """R-subset source for a template; literal chunks are appended to `texts` and referenced by index."""
     out: List[str] = []
     pos = 0
     for m in _TAG.finditer(text):
         lit = text[pos:m.start()]
         if lit:
+            lit = _Lit(lit)
+            lit.where = (path, text.count("\n", 0, m.start()) + 1)
             texts.append(lit)
             out.append(f".rt_text({len(texts) - 1})")
         kind, body = m.group(1) or "R", m.group(2)
@@ -109,7 +116,9 @@ def render(I: Interp, env: Env, path: str, search: Optional[List[str]] = None) -
     texts: List[str] = []
 
     def rt_text(I_, a, k):
-        I_.out.append(texts[int(scalar(a[0]))])
+        t = texts[int(scalar(a[0]))]
+        I_.out.append(t)
+        I_.rt_where = getattr(t, "where", None)
         return NULL
 
     def rt_fmt(I_, a, k):
@@ -129,7 +138,7 @@ def render(I: Interp, env: Env, path: str, search: Optional[List[str]] = None) -
         for d in search:
             p = os.path.join(d, name)
             if os.path.exists(p):
-                prog = template_to_program(_read(p), texts)
+                prog = template_to_program(_read(p), texts, p)
                 I_.run(prog, env)
                 return NULL
         raise RError(f"template include not found: {name}")
@@ -145,7 +154,13 @@ def render(I: Interp, env: Env, path: str, search: Optional[List[str]] = None) -
     saved = I.out
     I.out = []
     try:
-        I.run(template_to_program(_read(path), texts), env)
+        try:
+            I.run(template_to_program(_read(path), texts, path), env)
+        except Exception as e:
+            if not getattr(e, "rt_where", None):
+                e.rt_where = getattr(I, "rt_where", None)
+                e.args = (f"{e.args[0] if e.args else ''} (after the literal text ending at {e.rt_where})",) + e.args[1:]
+            raise
         return "".join(I.out)
     finally:
         I.out = saved

@@ -1,0 +1,8 @@
+: > gpurun_out/ab_kernel2.txt
+run() { echo "== $*" | tee -a gpurun_out/ab_kernel2.txt; env $1 python bench.py --steps 30 --warmup 5 ${@:2} 2>> gpurun_out/ab_kernel2.err | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['roofline']['fraction_of_measured_hbm'], d['clocks']['reasons'])" | tee -a gpurun_out/ab_kernel2.txt; }
+for g in "" "--no-globals"; do
+  run TCLB_KERNEL=classic $g
+  for lib in d3q27_cumulant d3q27_cumulant_pb5 d3q27_cumulant_pb6 d3q27_cumulant_pb8; do
+    for k in persist ring; do run TCLB_KERNEL=$k --model $lib $g; done
+  done
+done
