@@ -36,7 +36,26 @@ OUT = ROOT / "baseline" / "_ref"
 CUDA_HOME = Path(os.environ.get("CUDA_HOME", "/usr/local/cuda"))
 
 MODEL_DIRS = {"d3q27_cumulant": "flow/d3q27_cumulant", "d2q9": "flow/d2q9", "d3q19": "flow/d3q19",
-              "d3q27_pf_velocity": "multiphase/d3q27_pf_velocity"}
+              "d3q27_pf_velocity": "multiphase/d3q27_pf_velocity", "d3q19_heat": "heat/d3q19_heat",
+              "d2q9_poison_boltzmann": "electrokinetic/d2q9_poison_boltzmann"}
+
+
+def default_options(model: str, on=()) -> "OrderedDict":
+    """Options list of CLB/<model>/options.R: every option named in the model's conf.mk, switched on if listed in `on`
+    (src/models.R:28-66, src/makefile.main.Rt:143-163)"""
+    from tclb_b200.gen.rfrontend import all_option_names, parse_conf_mk
+    conf = parse_conf_mk(str(REF / "models" / MODEL_DIRS[model] / "conf.mk"))
+    opts = OrderedDict((o, (o in on)) for o in all_option_names(conf.get("OPT", "")))
+    if "autosym" in opts:
+        opts["autosym"] = 1 if "autosym" in on else 0
+    return opts
+
+
+def expand_one(model: str, template: str, on=()) -> str:
+    """text of one expanded reference template (e.g. "LatticeContainer.inc.cpp.Rt") for `model`"""
+    model_dir = REF / "models" / MODEL_DIRS[model]
+    src = REF / "src"
+    return render(model, model_dir, default_options(model, on), src / template, [REF / "tools", src, model_dir])
 
 
 def make_interp(model: str, model_dir: Path, options: dict, adjoint: int = 0):
@@ -189,8 +208,7 @@ if __name__ == "__main__":
     ap.add_argument("model", nargs="?", default="d3q27_cumulant")
     ap.add_argument("--expand-only", action="store_true")
     a = ap.parse_args()
-    opts = {"d3q27_cumulant": OrderedDict(AVG=False, IB=False, SMAG=False), "d2q9": OrderedDict(bc=False, autosym=0)}.get(a.model, OrderedDict())
-    d = expand(a.model, opts)
+    d = expand(a.model, default_options(a.model))
     print("expanded into", d)
     if not a.expand_only:
         print("built", compile_model(d))

@@ -31,6 +31,27 @@ sys.path.insert(0, ROOT)
 MODEL = "d3q27_cumulant"
 SHAPE = (1024, 512, 512)
 
+# BASELINE.json configs[1..4]; `--config cumulant` (configs[2]) is the headline and the default.
+#   walls: which faces are Wall nodes; globals: reduce the Globals every iteration (else never inside the timed loop)
+CONFIGS = {
+    "cumulant": dict(model="d3q27_cumulant", shape=(1024, 512, 512), walls="y", globals=True, scaling="strong",
+                     case="turbulent channel (y walls, body force), Globals every iteration"),
+    "d3q19": dict(model="d3q19", shape=(512, 512, 512), walls="xyz", globals=False, scaling="strong",
+                  case="closed Wall box driven by a body force (stand-in for the lid-driven cavity: the reference's d3q19 has no "
+                       "moving-wall node type, SURVEY 7.4)"),
+    "pf_velocity": dict(model="ref_d3q27_pf_velocity", shape=(512, 512, 512), walls="y", globals=False, scaling="strong",
+                        case="phase-field model lowered from the reference's own model files, 4-stage iteration, two lattices"),
+    "weak": dict(model="d3q27_cumulant", per_gpu=256, walls="y", globals=True, scaling="weak",
+                 case="weak-scaling halo sweep: PER_GPU^3 nodes per GPU (--per-gpu 128..384), Globals every iteration"),
+}
+
+
+def weak_shape(per_gpu: int, n: int):
+    """global lattice that gives every rank a per_gpu^3 block under the reference's decomposition rule
+    (y*z split minimising divz*ny + divy*nz, src/Solver.cpp.Rt:288-350): 2 -> 2x1, 4 -> 2x2, 8 -> 4x2 (y x z)"""
+    dy, dz = {1: (1, 1), 2: (2, 1), 4: (2, 2), 8: (4, 2)}.get(n, (n, 1))
+    return (per_gpu, per_gpu * dy, per_gpu * dz)
+
 
 REF_CASE = """<?xml version="1.0"?>
 <CLBConfig version="2.0" output="output/">
@@ -183,14 +204,24 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
+    ap.add_argument("--config", default="cumulant", choices=sorted(CONFIGS), help="named benchmark configuration of BASELINE.json")
+    ap.add_argument("--per-gpu", type=int, default=None, help="--config weak: edge of the cubic block each GPU owns (128..384)")
     ap.add_argument("--shape", default=None, help="nx,ny,nz override (diagnostics only; the headline uses 1024,512,512)")
-    ap.add_argument("--model", default=MODEL)
+    ap.add_argument("--model", default=None)
     ap.add_argument("--no-globals", action="store_true", help="diagnostics: skip the per-iteration Globals")
     ap.add_argument("--halo", default="direct", choices=["direct", "nccl"])
     ap.add_argument("--block", default=None, help="bx,by kernel block override")
     ap.add_argument("--no-graph", action="store_true", help="diagnostics: plain launches instead of the replayed CUDA graph")
     ap.add_argument("--precision", default="float", help="diagnostics: arithmetic[_storage] of the library (headline: float)")
     a = ap.parse_args()
+    cfg = CONFIGS[a.config]
+    if a.model is None:
+        a.model = cfg["model"]
+    if a.shape is None and a.config != "cumulant":
+        sh = weak_shape(a.per_gpu or cfg["per_gpu"], a.gpus) if cfg["scaling"] == "weak" else cfg["shape"]
+        a.shape = ",".join(str(v) for v in sh)
+    if not cfg["globals"]:
+        a.no_globals = True
     if a.impl == "reference":
         return reference_arm(a)
 
@@ -231,6 +262,14 @@ def main():
         fl[:, 0, :] = model.flag("Wall")
     if y0 + by_ == ny:
         fl[:, -1, :] = model.flag("Wall")
+    if "x" in cfg["walls"]:
+        fl[:, :, 0] = model.flag("Wall")
+        fl[:, :, -1] = model.flag("Wall")
+    if "z" in cfg["walls"]:
+        if z0 == 0:
+            fl[0, :, :] = model.flag("Wall")
+        if z0 + bz_ == nz:
+            fl[-1, :, :] = model.flag("Wall")
     dd.set_local_flags(fl)
     known = set(model.settings) | set(model.zonesettings)
     zonal_input = "Velocity" if "Velocity" in known else ("VelocityX" if "VelocityX" in known else None)
@@ -298,10 +337,10 @@ def main():
         out = {
             "metric": "MLUPS (whole box, device-timed, max over ranks)", "value": round(value, 1), "unit": "MLUPS",
             "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms_max / a.steps, 4),
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "higher_is_better": True, "scaling": cfg["scaling"], "vs_baseline": None,
             "dtype": "fp32" if a.precision == "float" else a.precision, "data": "synthetic",
             "impl": "ours",
-            "config": {"model": a.model, "case": "turbulent channel (y walls, body force), Globals every iteration" if use_globals else "no globals",
+            "config": {"name": a.config, "model": a.model, "case": cfg["case"] if (use_globals or not cfg["globals"]) else "no globals (diagnostic)",
                        "lattice": list(shape), "global_batch": int(nodes), "seq_len": None,
                        "parallelism": f"domain-decomposition y{d.divy}xz{d.divz}", "halo": "fused P2P stores" if a.halo == "direct" else "nccl baseline",
                        "l2": "working set 2x%.1f GB per job >> 126 MB L2, no flush needed" % (nodes * len(model.fields) * model.d.storage_size / 1e9)},

@@ -56,6 +56,7 @@ Adjoint::Adjoint(Domain *dom) : dom_(dom), lat_(nullptr) {
     rs_ = rs;
     dirs_ = dirs;
     sfn_ = (settings_fn)dlsym(lib_, "tclb_model_adjoint_settings");
+    zfn_ = (zsettings_fn)dlsym(lib_, "tclb_model_adjoint_zsettings");
     bytes_ = (size_t)m->d->n_fields * lat_->plane_elems * rs_;
     const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
     for (int i = 0; i < 2; i++) { adj_[i] = alloc(bytes_, dev); fill_zero(adj_[i]); }
@@ -73,6 +74,7 @@ Adjoint::~Adjoint() {
     const bool dev = lat_ && lat_->backend == TCLB_BACKEND_CUDA;
     for (int i = 0; i < 2; i++) if (adj_[i]) release(adj_[i], dev);
     if (sg_dev_) cudaFree(sg_dev_);
+    if (zg_dev_) cudaFree(zg_dev_);
     if (lib_) dlclose(lib_);
 }
 void *Adjoint::alloc(size_t bytes, bool device) const {
@@ -107,6 +109,7 @@ void Adjoint::drop_tape() {
 }
 void Adjoint::record(int n) {
     const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+    if (tape_.empty() && !zg_which_.empty()) clear_zone_gradients();
     const int obj = dom_->model->find_global("Objective");
     for (int i = 0; i < n; i++) {
         Frame f;
@@ -141,6 +144,7 @@ void Adjoint::step(const void *primal_in, int iter) {
     if (lat_->backend == TCLB_BACKEND_CUDA) ADJ_CUDA(cudaSetDevice(lat_->device));
     if (fn_(stage_, &L, out, in) != 0) fail("adjoint stage failed: %s", err_());
     if (!sg_which_.empty()) settings_pass(L, out);
+    if (!zg_which_.empty()) zsettings_pass(L, out, L.zone_index);
     if (tclb_adjoint_fold_ghosts(in, rs_, lat_->backend == TCLB_BACKEND_CUDA, dom_->model->d->n_fields, lat_->nx, lat_->ny, lat_->nz,
                                  lat_->gy, lat_->gz, lat_->stream) != 0)
         fail("adjoint: ghost fold failed");
@@ -194,6 +198,74 @@ void Adjoint::settings_pass(const tclb_launch_t &L, const void *adj_out) {
         const int n = (int)std::min((size_t)dirs_, sg_which_.size() - o);
         double *dst = dev ? sg_dev_ + o : sg_sum_.data() + o;
         if (sfn_(stage_, &L, adj_out, sg_which_.data() + o, n, dst) != 0) fail("adjoint settings pass failed: %s", err_());
+    }
+}
+void Adjoint::zg_resize() {
+    const int len = std::max(1, lat_->zs.len());
+    if (len == zg_len_ && zg_sum_.size() == (size_t)len * zg_which_.size() * 2) return;
+    zg_len_ = len;
+    zg_sum_.assign((size_t)len * zg_which_.size() * 2, 0.0);
+    if (lat_->backend == TCLB_BACKEND_CUDA) {
+        if (zg_dev_) cudaFree(zg_dev_);
+        ADJ_CUDA(cudaSetDevice(lat_->device));
+        ADJ_CUDA(cudaMalloc((void **)&zg_dev_, sizeof(double) * (zg_sum_.size() + dirs_)));
+        ADJ_CUDA(cudaMemset(zg_dev_, 0, sizeof(double) * (zg_sum_.size() + dirs_)));
+    }
+}
+void Adjoint::want_zone_gradient(int zonesetting, int zone) {
+    if (!zfn_) fail("adjoint: the adjoint library has no zonal-settings entry point (rebuild it)");
+    if (dirs_ < 2) fail("adjoint: zonal gradients need at least two tangent directions");
+    for (auto &p : zg_which_) if (p.first == zonesetting && p.second == zone) return;
+    zg_which_.push_back({zonesetting, zone});
+    zg_len_ = 0;
+    zg_resize();
+}
+void Adjoint::clear_zone_gradients() {
+    zg_len_ = 0;
+    if (!zg_which_.empty()) zg_resize();
+}
+void Adjoint::zsettings_pass(const tclb_launch_t &L, const void *adj_out, int time_level) {
+    zg_resize();
+    const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+    const size_t per_level = zg_which_.size() * 2;
+    const int pairs_per_pass = std::max(1, std::min(dirs_, 16) / 2);
+    for (size_t o = 0; o < zg_which_.size(); o += pairs_per_pass) {
+        const int np = (int)std::min((size_t)pairs_per_pass, zg_which_.size() - o);
+        int zs[16], zone[16], dt[16];
+        for (int k = 0; k < np; k++) {
+            zs[2 * k] = zs[2 * k + 1] = zg_which_[o + k].first;
+            zone[2 * k] = zone[2 * k + 1] = zg_which_[o + k].second;
+            dt[2 * k] = 0; dt[2 * k + 1] = 1;
+        }
+        double *dst = (dev ? zg_dev_ : zg_sum_.data()) + (size_t)time_level * per_level + 2 * o;
+        if (zfn_(stage_, &L, adj_out, zs, zone, dt, 2 * np, dst) != 0) fail("adjoint zonal-settings pass failed: %s", err_());
+    }
+}
+void Adjoint::zone_gradient(int zonesetting, int zone, double *out, int len) {
+    size_t k = 0;
+    for (; k < zg_which_.size(); k++) if (zg_which_[k].first == zonesetting && zg_which_[k].second == zone) break;
+    if (k == zg_which_.size()) fail("adjoint: the gradient of zonal setting %d in zone %d was not requested", zonesetting, zone);
+    if (lat_->backend == TCLB_BACKEND_CUDA && zg_dev_) {
+        ADJ_CUDA(cudaStreamSynchronize((cudaStream_t)lat_->stream));
+        ADJ_CUDA(cudaMemcpy(zg_sum_.data(), zg_dev_, sizeof(double) * zg_sum_.size(), cudaMemcpyDeviceToHost));
+    }
+    const size_t per_level = zg_which_.size() * 2;
+    const int L = zg_len_;
+    auto val = [&](int t) { return zg_sum_[(size_t)t * per_level + 2 * k]; };
+    auto ddt = [&](int t) { return zg_sum_[(size_t)t * per_level + 2 * k + 1]; };
+    if (len == 1) {               // a constant: every time level reads the same value, its central difference is zero
+        double s = 0;
+        for (int t = 0; t < L; t++) s += val(t);
+        out[0] = s;
+        return;
+    }
+    if (len != L) fail("adjoint: zone_gradient asked for %d time levels, the series has %d", len, L);
+    for (int t = 0; t < L; t++) out[t] = val(t);
+    // DT(t) = (v(t+1) - v(t-1)) / 2 with periodic wrap: transpose it
+    for (int t = 0; t < L; t++) {
+        const int ip = t + 1 < L ? t + 1 : 0, im = t > 0 ? t - 1 : L - 1;
+        out[ip] += 0.5 * ddt(t);
+        out[im] -= 0.5 * ddt(t);
     }
 }
 double Adjoint::setting_gradient(int setting) {

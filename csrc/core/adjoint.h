@@ -34,7 +34,22 @@ class Adjoint {
     // ---- gradients with respect to (non-zonal) settings, accumulated by reverse()/steady() ----
     void want_setting_gradients(const std::vector<int> &settings);   // call before record(); clears the sums
     double setting_gradient(int setting);        // total derivative: follows the derived-settings chain (nu -> omega ...)
+    // ---- gradients with respect to zonal settings, per time level of their series (reference: the gradient series of
+    // src/ZoneSettings.h:197-219, filled by the Tapenade adjoint; here by a tangent pass per reverse step) ----
+    void want_zone_gradient(int zonesetting, int zone);     // call before record(); keeps earlier requests
+    void clear_zone_gradients();                            // zero the sums (done by record() of a fresh tape)
+    // d Objective / d value(t), t = 0..len-1 (len = series length, 1 for a constant); the dependence through <name>_DT
+    // (central difference of the series) is folded back onto the neighbouring time levels
+    void zone_gradient(int zonesetting, int zone, double *out, int len);
   private:
+    typedef int (*zsettings_fn)(int, const tclb_launch_t *, const void *, const int *, const int *, const int *, int, double *);
+    zsettings_fn zfn_ = nullptr;
+    std::vector<std::pair<int, int>> zg_which_;      // (zonal setting, zone)
+    std::vector<double> zg_sum_;                     // [time level][pair][value, dt]
+    double *zg_dev_ = nullptr;
+    int zg_len_ = 0;
+    void zsettings_pass(const tclb_launch_t &L, const void *adj_out, int time_level);
+    void zg_resize();
     typedef int (*settings_fn)(int, const tclb_launch_t *, const void *, const int *, int, double *);
     settings_fn sfn_ = nullptr;
     int dirs_ = 4;

@@ -177,6 +177,7 @@ int tclb_domain_set_block(tclb_domain_h *h, int bx, int by) {
     for (int r : h->d->local) { h->d->lat[r]->block_x = bx; h->d->lat[r]->block_y = by; }
     GUARD_END_INT
 }
+int tclb_domain_pri_blocks(tclb_domain_h *h, int rank, long long *out27) { GUARD_BEGIN rank_lat(h, rank)->pri_block_elems(out27); GUARD_END_INT }
 int tclb_domain_save_pri(tclb_domain_h *h, int rank, const char *f) { GUARD_BEGIN rank_lat(h, rank)->save_pri(f); GUARD_END_INT }
 int tclb_domain_load_pri(tclb_domain_h *h, int rank, const char *f) { GUARD_BEGIN rank_lat(h, rank)->load_pri(f); GUARD_END_INT }
 void *tclb_domain_snapshot_ptr(tclb_domain_h *h, int rank, int snap, int64_t shape[4], int *gy, int *gz, int *current) {

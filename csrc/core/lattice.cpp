@@ -109,11 +109,14 @@ Lattice::~Lattice() {
         if (zone_dev_) cudaFree(zone_dev_);
         if (cuts_dev_) cudaFree(cuts_dev_);
         if (particles_dev_) cudaFree(particles_dev_);
+        if (pgrid_dev_) cudaFree(pgrid_dev_);
+        if (pgrid_counts_) cudaFree(pgrid_counts_);
+        if (pgrid_overflow_) cudaFree(pgrid_overflow_);
         if (st_dev_) cudaFree(st_dev_);
         if (scratch_) cudaFree(scratch_);
         if (pinned_) cudaFreeHost(pinned_);
     } else {
-        free(zone_dev_); free(cuts_dev_); free(st_dev_); free(scratch_); free(particles_dev_);
+        free(zone_dev_); free(cuts_dev_); free(st_dev_); free(scratch_); free(particles_dev_); free(pgrid_dev_); free(pgrid_counts_); free(pgrid_overflow_);
     }
 }
 
@@ -166,9 +169,62 @@ void Lattice::set_particles(const std::vector<double> &rows) {
         particles_cap_ = n * 2;
     }
     n_particles_ = n;
+    pgrid_on_ = false;
     if (n == 0) return;
     if (rs == 4) { std::vector<float> f(rows.begin(), rows.end()); to_dev(particles_dev_, f.data(), f.size() * 4); }
     else to_dev(particles_dev_, rows.data(), rows.size() * 8);
+    build_particle_grid(rows);
+}
+extern "C" int tclb_particle_grid_fill(const void *rows, int n, int real_size, const double *origin, double inv_delta, const int *gn,
+                                       int depth, int *grid, int *counts, int *overflow, int on_device, void *stream);
+// Container over the particle table (TCLB_SOLID_CONTAINER=all switches it off, like the reference's
+// --with-solid-container=all): cell edge = 2 * (largest radius + margin), so a node looks at 2 cells per axis.
+void Lattice::build_particle_grid(const std::vector<double> &rows) {
+    const char *sel = getenv("TCLB_SOLID_CONTAINER");
+    if (sel && !strcmp(sel, "all")) return;
+    const int n = n_particles_;
+    if (model->d->part_margin > 0) part_margin = model->d->part_margin;
+    double rmax = 0;
+    for (int i = 0; i < n; i++) rmax = std::max(rmax, rows[(size_t)i * 16]);
+    const double delta = 2.0 * (rmax + part_margin) * (1.0 + 1e-6) + 1e-9;
+    const int nn[3] = {nx, ny, nz};
+    const double lo[3] = {region.x0 + origin[0] + 0.5, region.y0 + origin[1] + 0.5, region.z0 + origin[2] + 0.5};
+    size_t cells = 1;
+    for (int k = 0; k < 3; k++) {
+        pg_origin_[k] = lo[k] - delta;              // one cell of room around the nodes of this subdomain
+        pg_n_[k] = (int)std::ceil((nn[k] - 1 + 2.0 * delta) / delta) + 1;
+        cells *= (size_t)pg_n_[k];
+    }
+    pg_inv_delta_ = 1.0 / delta;
+    const bool dev = backend == TCLB_BACKEND_CUDA;
+    for (int attempt = 0; attempt < 12; attempt++) {
+        if (cells * pg_depth_ > pgrid_cap_ || cells > pgrid_cells_cap_) {
+            if (dev) {
+                TCLB_CUDA(cudaSetDevice(device));
+                sync();
+                if (pgrid_dev_) cudaFree(pgrid_dev_);
+                if (pgrid_counts_) cudaFree(pgrid_counts_);
+                if (!pgrid_overflow_) TCLB_CUDA(cudaMalloc((void **)&pgrid_overflow_, sizeof(int)));
+                TCLB_CUDA(cudaMalloc((void **)&pgrid_dev_, cells * pg_depth_ * sizeof(int)));
+                TCLB_CUDA(cudaMalloc((void **)&pgrid_counts_, cells * sizeof(int)));
+            } else {
+                free(pgrid_dev_); free(pgrid_counts_);
+                if (!pgrid_overflow_) pgrid_overflow_ = (int *)malloc(sizeof(int));
+                pgrid_dev_ = (int *)malloc(cells * pg_depth_ * sizeof(int));
+                pgrid_counts_ = (int *)malloc(cells * sizeof(int));
+            }
+            pgrid_cap_ = cells * pg_depth_;
+            pgrid_cells_cap_ = cells;
+        }
+        if (tclb_particle_grid_fill(particles_dev_, n, model->real_size(), pg_origin_, pg_inv_delta_, pg_n_, pg_depth_, pgrid_dev_,
+                                    pgrid_counts_, pgrid_overflow_, dev ? 1 : 0, stream) != 0)
+            fail("particle grid build failed");
+        int over = 0;
+        to_host(&over, pgrid_overflow_, sizeof(int));
+        if (!over) { pgrid_on_ = true; return; }
+        pg_depth_ *= 2;                              // a cell holds more particles than slots: deeper cells, again
+    }
+    logf(L_WARNING, "particle grid: cells stay overfull, falling back to the scan over every particle");
 }
 void Lattice::get_particles(std::vector<double> &rows) {
     const int rs = model->real_size();
@@ -453,6 +509,9 @@ void Lattice::fill_launch(tclb_launch_t &L) const {
     L.st_modes = (const tclb_st_mode_t *)st_dev_; L.st_n = st_n_;
     L.block_x = block_x; L.block_y = block_y;
     L.particles = particles_dev_; L.n_particles = n_particles_;
+    L.pgrid = pgrid_on_ ? pgrid_dev_ : nullptr;
+    for (int k = 0; k < 3; k++) { L.pg_n[k] = pg_n_[k]; L.pg_origin[k] = pg_origin_[k]; }
+    L.pg_depth = pg_depth_; L.pg_inv_delta = pg_inv_delta_;
     L.scale = 1.0;
     L.obj_enabled = obj_enabled_ ? 1 : 0;
 }

@@ -124,6 +124,8 @@ class Lattice {
     void set_particles(const std::vector<double> &rows16);
     void get_particles(std::vector<double> &rows16);        // after the particle stages: force/moment filled in
     int n_particles() const { return n_particles_; }
+    double part_margin = 0.5;         // reach of a particle beyond its radius (model's PartMargin), set by the solver
+    int particle_grid_depth() const { return pgrid_on_ ? pg_depth_ : 0; }
     // ---- execution ----
     void launch_stage(int stage, int in_snap, int out_snap, int globals_mode, bool publish_globals = true);
     void clear_globals();
@@ -137,6 +139,7 @@ class Lattice {
     void save_pri(const std::string &file) const;
     void load_pri(const std::string &file);
     size_t pri_bytes() const;
+    void pri_block_elems(long long out[27]) const;      // elements of each of the 27 margin blocks of the image (0 = absent)
     bool has_nan(int q, const Box &local_box);
 
   private:
@@ -160,6 +163,13 @@ class Lattice {
     int *dyn_dev_ = nullptr;          // device int[2]: iteration and epoch at the start of a replayed graph
     void *particles_dev_ = nullptr;   // real_t[n_particles_][16]
     int n_particles_ = 0, particles_cap_ = 0;
+    // uniform-grid container over the particles (csrc/kernels/particle_grid.cu; reference SolidGrid), rebuilt by set_particles
+    int *pgrid_dev_ = nullptr, *pgrid_counts_ = nullptr, *pgrid_overflow_ = nullptr;
+    size_t pgrid_cap_ = 0, pgrid_cells_cap_ = 0;
+    int pg_n_[3] = {0, 0, 0}, pg_depth_ = 4;
+    double pg_origin_[3] = {0, 0, 0}, pg_inv_delta_ = 0;
+    bool pgrid_on_ = false;
+    void build_particle_grid(const std::vector<double> &rows16);
     bool owns_stream_ = false;
     void *pinned_ = nullptr;       // page-locked staging: [0,half) host->device, [half,end) device->host
     size_t pinned_bytes_ = 0;

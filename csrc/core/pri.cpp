@@ -40,6 +40,15 @@ size_t Lattice::pri_bytes() const {
     return tot * model->storage_size();       // the image holds storage_t values, like the reference's checkpoints
 }
 
+void Lattice::pri_block_elems(long long out[27]) const {
+    BlockField p;
+    for (int m = 0; m < 27; m++) {
+        out[m] = 0;
+        for (int k = 0; k < model->d->n_fields; k++)
+            if (piece(*this, m, k, p)) out[m] += (long long)p.elems;
+    }
+}
+
 template <class T, bool SAVE>
 static void pri_transfer(const Lattice &L, T *slab, T *image) {
     size_t pos = 0;

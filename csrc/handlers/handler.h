@@ -13,7 +13,7 @@
 namespace tclb {
 
 enum { HANDLER_CALLBACK = 0x01, HANDLER_ACTION = 0x02, HANDLER_DESIGN = 0x04, HANDLER_CONTAINER = 0x08 };
-enum { PAR_GET = 0, PAR_SET = 1, PAR_GRAD = 2, PAR_UPPER = 3, PAR_LOWER = 4 };
+enum { PAR_GET = 0, PAR_SET = 1, PAR_GRAD = 2, PAR_UPPER = 3, PAR_LOWER = 4, PAR_X = 5, PAR_Y = 6, PAR_Z = 7, PAR_T = 8 };
 
 class Handler {
   public:

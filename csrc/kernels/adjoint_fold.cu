@@ -62,3 +62,24 @@ extern "C" int tclb_adjoint_fold_ghosts(void *adj, int real_size, int on_device,
     else k_fold_ghosts<float><<<grid, tb, 0, (cudaStream_t)stream>>>((float *)adj, nx, ny, nz, gy, gz);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
+
+// dst += src over n values (adjoint buffers of the intermediate stages of a multi-stage action are merged with this)
+namespace {
+template <class T>
+__global__ void k_add_into(T *dst, const T *src, long long n) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const T v = src[i]; if (v != (T)0) dst[i] += v; }
+}
+}  // namespace
+extern "C" int tclb_adjoint_add_into(void *dst, const void *src, long long n, int real_size, int on_device, void *stream) {
+    if (!on_device) {
+        if (real_size == 8) { double *d = (double *)dst; const double *s = (const double *)src; for (long long i = 0; i < n; i++) d[i] += s[i]; }
+        else { float *d = (float *)dst; const float *s = (const float *)src; for (long long i = 0; i < n; i++) d[i] += s[i]; }
+        return 0;
+    }
+    const int tb = 256;
+    const long long nb = (n + tb - 1) / tb;
+    if (real_size == 8) k_add_into<double><<<(unsigned)nb, tb, 0, (cudaStream_t)stream>>>((double *)dst, (const double *)src, n);
+    else k_add_into<float><<<(unsigned)nb, tb, 0, (cudaStream_t)stream>>>((float *)dst, (const float *)src, n);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}

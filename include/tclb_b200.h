@@ -55,6 +55,8 @@ int tclb_domain_set_block(tclb_domain_h *, int bx, int by);
 int tclb_domain_use_graphs(tclb_domain_h *, int on);
 long long tclb_domain_graph_iterations(tclb_domain_h *);
 int tclb_domain_save_pri(tclb_domain_h *, int rank, const char *file);
+/* elements of the 27 margin blocks of a rank's checkpoint image, in file order (reference: src/conf.R:897-999 MarginSizes) */
+int tclb_domain_pri_blocks(tclb_domain_h *, int rank, long long *out27);
 int tclb_domain_load_pri(tclb_domain_h *, int rank, const char *file);
 /* raw device views for DLPack/torch coupling: base pointer of the CURRENT snapshot of a rank and its shape
  * [n_fields][nz+2gz][ny+2gy][nx]; `snap`<0 means current */

@@ -12,7 +12,7 @@
 extern "C" {
 #endif
 
-#define TCLB_ABI_VERSION 9
+#define TCLB_ABI_VERSION 10
 #define TCLB_MAX_NEIGH 9            /* (dy,dz) in {-1,0,1}^2 ; x is never decomposed */
 #define TCLB_MAX_RANKS 16           /* subdomains that exchange Globals through peer memory (one box) */
 #define TCLB_GL_RING 8              /* depth of the Globals publication ring */
@@ -86,8 +86,11 @@ typedef struct {
     const tclb_st_mode_t *st_modes; int st_n;
     /* block shape request (0 = model default) */
     int block_x, block_y;
-    /* particles (later phases) */
+    /* particles: rows of 16 real_t (r, pos, vel, angular vel, force, moment); optional uniform-grid container over them:
+     * pgrid = int[pg_n[2]][pg_n[1]][pg_n[0]][pg_depth] particle indices (-1 = empty slot), cell of a position p is
+     * floor((p - pg_origin) * pg_inv_delta) per axis; NULL = look at every particle */
     const void *particles; int n_particles;
+    const int *pgrid; int pg_n[3]; int pg_depth; double pg_origin[3]; double pg_inv_delta;
     /* CUDA-graph launches: device int[2] = {iteration, epoch} at the start of the graph + this launch's constant offsets */
     const int *dyn; int dyn_iter_off; unsigned dyn_epoch_off;
 } tclb_launch_t;
@@ -120,6 +123,7 @@ typedef struct {
     int storage_size, storage_shifted;
     const char *storage_name;
     const double *field_shift;
+    double part_margin;                  /* reach of a particle beyond its radius in the particle stages (model's PartMargin) */
 } tclb_model_t;
 
 /* every model library exports exactly this symbol */

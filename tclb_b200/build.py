@@ -228,9 +228,12 @@ def build_custom(modeldef, libname: str, precision: str = "double", extra_flags=
     GENDIR.mkdir(parents=True, exist_ok=True)
     LIBDIR.mkdir(parents=True, exist_ok=True)
     src = GENDIR / f"{libname}.cu"
-    text = emit_model_source(modeldef, libname)
-    if not src.exists() or src.read_text() != text:
-        src.write_text(text)
+    with _GEN_LOCK:          # float and double builds of one library share this file
+        text = emit_model_source(modeldef, libname)
+        if not src.exists() or src.read_text() != text:
+            tmp = src.with_suffix(".cu.tmp")
+            tmp.write_text(text)
+            os.replace(tmp, src)
     target = LIBDIR / f"libtclb_{libname}_{precision}.so"
     hdrs = [ROOT / "include" / "tclb_model_abi.h", ROOT / "csrc" / "kernels" / "tclb_node_rt.h"]
     digest = _hash([src] + hdrs, precision + " ".join(NVCC_FLAGS + ARCH_FLAGS + list(extra_flags)))
@@ -263,7 +266,7 @@ def build_from_dir(model_dir: str, name: Optional[str] = None, precision: str = 
     from .gen import rfrontend
     with _GEN_LOCK:
         m = rfrontend.load_model(model_dir, name=name, options=options)
-    on = [k for k, v in (options or {}).items() if v]
+    on = [k + (str(int(v)) if not isinstance(v, bool) and int(v) > 1 else "") for k, v in (options or {}).items() if v]
     lib = libname or "ref_" + "_".join([m.name] + on)
     _CUSTOM_MODELS[lib] = lambda: rfrontend.load_model(model_dir, name=name, options=options)
     return build_custom(m, lib, precision)
@@ -277,22 +280,32 @@ REFERENCE_MODELS = ["multiphase/d3q27_pf_velocity", "flow/d2q9", "flow/d3q19", "
 REFERENCE_ADJOINT = ["ref_d2q9_adj"]             # libraries that also get their adjoint companion (build_adjoint_lib)
 
 
-def build_reference_models(precisions=("float", "double"), verbose=False) -> List[Path]:
-    out = []
+def build_reference_models(precisions=("float", "double"), verbose=False, jobs=None) -> List[Path]:
+    """Libraries lowered from the mounted reference tree's own model directories.  Front-end and source generation run one
+    at a time (shared symbolic state, _GEN_LOCK); the nvcc compilations run side by side."""
+    out: List[Path] = []
     if not (REFERENCE_ROOT / "models").is_dir():
         return out
+    tasks = []
     for entry in REFERENCE_MODELS:
         rel, _, optlist = entry.partition(":")
         d = REFERENCE_ROOT / "models" / rel
-        if not d.is_dir():
-            continue
-        for p in precisions:
-            out.append(build_from_dir(str(d), precision=p, options={o: True for o in optlist.split(",") if o}))
-            if verbose:
-                print(f"built {out[-1]}")
-            name = out[-1].name[len("libtclb_"):-len(f"_{p}.so")]
-            if name in REFERENCE_ADJOINT:
-                out.append(build_adjoint_lib(name, p))
+        if d.is_dir():
+            tasks += [(d, p, {o: True for o in optlist.split(",") if o}) for p in precisions]
+
+    def one(t):
+        d, p, opts = t
+        res = [build_from_dir(str(d), precision=p, options=opts)]
+        if verbose:
+            print(f"built {res[0]}")
+        name = res[0].name[len("libtclb_"):-len(f"_{p}.so")]
+        if name in REFERENCE_ADJOINT:
+            res.append(build_adjoint_lib(name, p))
+        return res
+
+    with cf.ThreadPoolExecutor(max_workers=jobs or max(1, (os.cpu_count() or 4))) as ex:
+        for res in ex.map(one, tasks):
+            out += res
     return out
 
 

@@ -120,7 +120,8 @@ _PARTICLES = r"""
 #define RFI_DATA_FORCE 10
 #define RFI_DATA_MOMENT 13
 #define RFI_DATA_SIZE 16
-#define PART_MAR ((real_t)@PART_MAR@)
+#define PART_MAR_VALUE @PART_MAR@
+#define PART_MAR ((real_t)PART_MAR_VALUE)
 TCLB_HD void particle_atomic_add(base_t *p, real_t v_) {
     const base_t v = tclb_value(v_);
 #ifdef __CUDA_ARCH__
@@ -169,11 +170,32 @@ struct ParticleS : ParticleI {
         particle_atomic_add(row + RFI_DATA_MOMENT + 2, moment.z);
     }
 };
+// Range over the particles that can touch the node at (x,y,z): through the uniform-grid container when the runtime built
+// one (reference SolidGrid: the two cells per axis around the node, `depth` slots each), else over every particle
+// (reference SolidAll).  Either way a particle is handed out only if its padded bounding box contains the node.
 template <class P>
 struct ParticleRange {
     base_t *data;
     int n;
     real_t x, y, z;
+    const int *grid;
+    int gn0, gn1, gn2, depth, lo0, lo1, lo2, hi0, hi1, hi2;
+    TCLB_HD ParticleRange(base_t *data_, int n_, real_t x_, real_t y_, real_t z_, const int *grid_, const int *gn, int depth_,
+                          const double *org, double inv_delta) : data(data_), n(n_), x(x_), y(y_), z(z_), grid(grid_) {
+        gn0 = gn[0]; gn1 = gn[1]; gn2 = gn[2]; depth = depth_;
+        lo0 = lo1 = lo2 = hi0 = hi1 = hi2 = 0;
+        if (grid) {
+            const double p[3] = {(double)tclb_value(x), (double)tclb_value(y), (double)tclb_value(z)};
+            int lo[3], hi[3];
+            for (int k = 0; k < 3; k++) {
+                const double c = (p[k] - org[k]) * inv_delta;
+                lo[k] = (int)floor(c - 0.5); hi[k] = (int)floor(c + 0.5);
+                if (lo[k] < 0) lo[k] = 0;
+                if (hi[k] >= gn[k]) hi[k] = gn[k] - 1;
+            }
+            lo0 = lo[0]; lo1 = lo[1]; lo2 = lo[2]; hi0 = hi[0]; hi1 = hi[1]; hi2 = hi[2];
+        }
+    }
     TCLB_HD bool near(int i) const {
         const base_t *row = data + (size_t)i * RFI_DATA_SIZE;
         const real_t rr = row[RFI_DATA_R] + PART_MAR;
@@ -181,16 +203,99 @@ struct ParticleRange {
     }
     struct It {
         const ParticleRange *r;
-        int i;
-        TCLB_HD void skip() { while (i < r->n && !r->near(i)) i++; }
+        int i;                 // particle index, r->n = end
+        int c0, c1, c2, d;     // grid walk: cell and slot
+        TCLB_HD void skip() {
+            if (!r->grid) { while (i < r->n && !r->near(i)) i++; return; }
+            for (; c2 <= r->hi2; c2++, c1 = r->lo1) {
+                for (; c1 <= r->hi1; c1++, c0 = r->lo0) {
+                    for (; c0 <= r->hi0; c0++, d = 0) {
+                        const int *cell = r->grid + (((size_t)c2 * r->gn1 + c1) * r->gn0 + c0) * r->depth;
+                        for (; d < r->depth; d++) {
+                            const int k = cell[d];
+                            if (k < 0) break;             // slots fill from the front
+                            if (r->near(k)) { i = k; return; }
+                        }
+                    }
+                }
+            }
+            i = r->n;
+        }
         TCLB_HD P operator*() const { return P(r->data + (size_t)i * RFI_DATA_SIZE, r->x, r->y, r->z); }
-        TCLB_HD It &operator++() { i++; skip(); return *this; }
+        TCLB_HD It &operator++() { if (r->grid) d++; else i++; skip(); return *this; }
         TCLB_HD bool operator!=(const It &o) const { return i != o.i; }
     };
-    TCLB_HD It begin() const { It it{this, 0}; it.skip(); return it; }
-    TCLB_HD It end() const { return It{this, n}; }
+    TCLB_HD It begin() const { It it{this, 0, lo0, lo1, lo2, 0}; if (n == 0 || (grid && (lo0 > hi0 || lo1 > hi1 || lo2 > hi2))) it.i = n; else it.skip(); return it; }
+    TCLB_HD It end() const { return It{this, n, 0, 0, 0, 0}; }
+};
+// the older iterator form of model code: for (ParticleIterator p(X,Y,Z); p; ++p) { ... p.diff ... p.applyForce(f); }
+// (rewritten by the generator to OldParticleIterator<...> p(*this, X,Y,Z)); the object is the range, its iterator and
+// the current particle at once
+struct ParticleDummyRow {
+    base_t zero_row[RFI_DATA_SIZE];
+    TCLB_HD ParticleDummyRow() { for (int i = 0; i < RFI_DATA_SIZE; i++) zero_row[i] = 0; }
+};
+template <class P>
+struct ParticleRangeHolder {
+    ParticleRange<P> range;
+    typename ParticleRange<P>::It it;
+    TCLB_HD ParticleRangeHolder(const ParticleRange<P> &r) : range(r), it(range.begin()) {}
+    TCLB_HD base_t *row(base_t *dummy) const { return it != range.end() ? range.data + (size_t)it.i * RFI_DATA_SIZE : dummy; }
+};
+template <class P, class N>
+struct OldParticleIterator : ParticleDummyRow, ParticleRangeHolder<P>, P {
+    typedef ParticleRangeHolder<P> H;
+    TCLB_HD OldParticleIterator(const N &node, real_t x, real_t y, real_t z)
+        : ParticleDummyRow(), H(node.template particle_range<P>(x, y, z)), P(H::row(this->zero_row), x, y, z) {}
+    TCLB_HD operator bool() const { return H::it != H::range.end(); }
+    TCLB_HD OldParticleIterator &operator++() {
+        static_cast<P *>(this)->~P();              // a ParticleS hands its force to the table here
+        ++H::it;
+        new (static_cast<P *>(this)) P(H::row(this->zero_row), H::range.x, H::range.y, H::range.z);
+        return *this;
+    }
 };
 """
+
+
+def _autosym_resolve(m: ModelDef, s, fidx) -> str:
+    """what follows the plain pull of a stage under option autosym (reference SymmetryAccess::pop,
+    src/LatticeAccess.inc.cpp.Rt:449-475 and resolve.symmetries :229-256)"""
+    mode = int(getattr(m, "autosym", 0) or 0)
+    if not mode:
+        return ""
+    L = []
+    axes = "XYZ"
+    have = {n.group for n in m.nodetypes}
+    loaded = [d for d in m.densities if d.load.get(s.name) and not d.adjoint]
+    if mode == 1:
+        # mirror plane through the node: populations that would come from beyond it are the mirror partners held by this node
+        for ax in range(3):
+            if f"SYM{axes[ax]}" not in have:
+                continue
+            comp = lambda d: (d.dx, d.dy, d.dz)[ax]
+            plus = [d for d in loaded if comp(d) < 0]
+            minus = [d for d in loaded if comp(d) > 0]
+            if not plus and not minus:
+                continue
+            L.append(f"    switch (n.n_type & NODE_SYM{axes[ax]}) {{")
+            for tag, sel in (("plus", plus), ("minus", minus)):
+                if sel:
+                    L.append(f"    case NODE_{m.autosym_name}{axes[ax]}_{tag}:")
+                    for d in sel:
+                        p = d.sym[ax]
+                        L.append(f"        n.{d.name} = {'-' if p.startswith('-') else ''}n.{p.lstrip('-')};")
+                    L.append("        break;")
+            L.append("    }")
+    else:
+        # mirror plane on the cell edge: on a symmetry node every population is pulled through the redirecting accessor
+        groups = " | ".join(f"NODE_SYM{axes[ax]}" for ax in range(3) if f"SYM{axes[ax]}" in have)
+        if groups:
+            L.append(f"    if (n.n_type & ({groups})) {{")
+            for d in loaded:
+                L.append(f"        n.{d.name} = n.load_field({fidx[d.field]}, {-d.dx}, {-d.dy}, {-d.dz});")
+            L.append("    }")
+    return "\n".join(L)
 
 
 def emit_model_source(m: ModelDef, libname: str, adjoint: bool = False) -> str:
@@ -210,7 +315,7 @@ def emit_model_source(m: ModelDef, libname: str, adjoint: bool = False) -> str:
     L: List[str] = []
     A = L.append
     A(f"// GENERATED by tclb_b200.gen.emit -- model {m.name} ({libname}); do not edit.")
-    A('#include "tclb_node_rt.h"')
+    A('#include <new>\n#include "tclb_node_rt.h"')
     A("#ifdef TCLB_DOUBLE\ntypedef double base_t;\n#define TCLB_REAL_NAME \"double\"\n#else\ntypedef float base_t;\n#define TCLB_REAL_NAME \"float\"\n#endif")
     # adjoint build (-DTCLB_AD, csrc/kernels/tclb_dual.h): the node code computes in dual numbers, memory stays base_t
     A("#ifdef TCLB_AD\n#include \"tclb_dual.h\"\ntypedef Dual<base_t, TCLB_AD_DIRS> real_t;\n#else\ntypedef base_t real_t;\n#endif")
@@ -264,6 +369,12 @@ typedef base_t storage_t;
         # separate bound for the kernel variants that also reduce Globals (they need a few more registers)
         A("#ifndef TCLB_MIN_BLOCKS_G\n#ifdef TCLB_DOUBLE\n#define TCLB_MIN_BLOCKS_G %d\n#else\n#define TCLB_MIN_BLOCKS_G %d\n#endif\n#endif"
           % (int(tun.get("min_blocks_g_double", tun.get("min_blocks_double", 0))), int(tun.get("min_blocks_g_float", tun.get("min_blocks_float", 0)))))
+    # which stage kernel a launch uses unless TCLB_KERNEL says otherwise (0 one block per tile, 1 persistent, 2 persistent +
+    # bulk-copy ring), separately for launches without / with Globals, and the occupancy the persistent kernels are built for
+    A("#ifndef TCLB_KERNEL_DEFAULT\n#define TCLB_KERNEL_DEFAULT %d\n#endif" % int(tun.get("kernel", 0)))
+    A("#ifndef TCLB_KERNEL_DEFAULT_G\n#define TCLB_KERNEL_DEFAULT_G %d\n#endif" % int(tun.get("kernel_g", 2)))
+    A("#ifndef TCLB_PERSIST_MIN_BLOCKS\n#ifdef TCLB_DOUBLE\n#define TCLB_PERSIST_MIN_BLOCKS %d\n#else\n#define TCLB_PERSIST_MIN_BLOCKS %d\n#endif\n#endif"
+      % (int(tun.get("persist_min_blocks_double", 3)), int(tun.get("persist_min_blocks_float", 5))))
     A("namespace {")
     A(f"constexpr int N_FIELDS={nf}, N_DENSITIES={nd}, N_SETTINGS={ns}, N_ZONESETTINGS={nzs}, N_GLOBALS={ng}, N_QUANTITIES={nq};")
     A(f"constexpr int SUM_GLOBALS={m.sum_globals}, IN_OBJ_OFFSET={m.in_obj_offset}, GLOBALS_Objective={obj_idx};")
@@ -326,11 +437,17 @@ struct KArgs {
     int st_n;
     base_t *particles;           // [n_particles][16]: r, pos, vel, angular velocity, force, moment (RFI layout)
     int n_particles;
+    const int *pgrid;            // uniform-grid container over the particles (NULL: scan all), see tclb_launch_t
+    int pg_n[3], pg_depth;
+    double pg_origin[3], pg_inv_delta;
     // launches captured in a CUDA graph take iteration and halo epoch from device memory (dyn[0], dyn[1] = values at
     // the start of the graph) plus a constant offset, so one instantiated graph can be replayed; NULL otherwise
     const int *dyn;
     int dyn_iter_off;
     unsigned dyn_epoch_off;
+    // adjoint build, gradient with respect to zonal settings: tangent direction j is seeded where the node code reads
+    // zonal setting ad_zs_set[j] in zone ad_zs_zone[j] (ad_zs_dt[j] = 0: the value, 1: its _DT time derivative); -1 = unused
+    short ad_zs_set[16], ad_zs_zone[16], ad_zs_dt[16];
     real_t settings[N_SETTINGS > 0 ? N_SETTINGS : 1];
 };
 // Kernel variant bit 4 (GMODE & 4) = "launched from a captured graph": only that variant reads the device-resident
@@ -392,6 +509,34 @@ template <int GMODE> TCLB_HD int k_zone_index(const KArgs &a) {
             A(f"    case {i}: return (real_t){float(f.shift)!r};")
     A("    default: return (real_t)0;\n    }\n}")
 
+    autosym = int(getattr(m, "autosym", 0) or 0)
+    A(f"#define TCLB_AUTOSYM {autosym}")
+    if autosym:
+        A(f"#define TCLB_AUTOSYM_SHIFT {int(m.autosym_shift)}")
+        axes = "XYZ"
+        def nt(name):
+            r = [n for n in m.nodetypes if n.name == name]
+            return r[0] if r else None
+        for what, suf in (("mask", None), ("plus", "_plus"), ("minus", "_minus")):
+            A(f"TCLB_HD unsigned t_sym_{what}(int ax) {{\n    switch (ax) {{")
+            for ax in range(3):
+                n_ = nt(f"{m.autosym_name}{axes[ax]}_plus")
+                if n_ is None:
+                    continue
+                val = n_.mask if suf is None else nt(f"{m.autosym_name}{axes[ax]}{suf}").value
+                A(f"    case {ax}: return {val}u;")
+            A("    default: return 0u;\n    }\n}")
+        A("TCLB_HD int t_sym_field(int fi, int ax) {\n    switch (fi * 3 + ax) {")
+        for i, f in enumerate(m.fields):
+            for ax in range(3):
+                A(f"    case {i * 3 + ax}: return {fidx[f.sym[ax].lstrip('-')]};")
+        A("    default: return fi;\n    }\n}")
+        A("TCLB_HD real_t t_sym_sign(int fi, int ax) {\n    switch (fi * 3 + ax) {")
+        for i, f in enumerate(m.fields):
+            for ax in range(3):
+                if f.sym[ax].startswith("-"):
+                    A(f"    case {i * 3 + ax}: return (real_t)-1;")
+        A("    default: return (real_t)1;\n    }\n}")
     members = _member_decls([d.name for d in m.densities] + [f.name for f in m.fields])
     A(r"""
 #ifdef __CUDA_ARCH__
@@ -432,30 +577,62 @@ struct Node {
         if s.name in member_zs:
             A(f"        {s.name} = zone_setting({i});")
     A(r"""    }
+#ifdef TCLB_AD
+    TCLB_HD void ad_seed_zone(real_t &v, int s, int dt) const {
+        const int zn = (int)(n_type >> ZONE_SHIFT);
+        for (int j = 0; j < TCLB_AD_DIRS && j < 16; j++)
+            if (ka_.ad_zs_set[j] == s && ka_.ad_zs_zone[j] == zn && ka_.ad_zs_dt[j] == dt) v.d[j] = 1;
+    }
+#endif
     TCLB_HD real_t zone_setting(int s) const {
         // the table is tiny (time levels x settings x zones): 32-bit index arithmetic
-        return ka_.zone[(k_zone_index<GMODE>(ka_) * N_ZONESETTINGS + s) * ka_.zone_stride + (int)(n_type >> ZONE_SHIFT)];
+        real_t v = ka_.zone[(k_zone_index<GMODE>(ka_) * N_ZONESETTINGS + s) * ka_.zone_stride + (int)(n_type >> ZONE_SHIFT)];
+#ifdef TCLB_AD
+        ad_seed_zone(v, s, 0);
+#endif
+        return v;
     }
     TCLB_HD real_t zone_setting_dt(int s) const {
         const int zi = k_zone_index<GMODE>(ka_);
         int ip = zi + 1 < ka_.zone_len ? zi + 1 : 0;
         int im = zi > 0 ? zi - 1 : ka_.zone_len - 1;
         int zn = n_type >> ZONE_SHIFT;
-        return (ka_.zone[((long long)ip * N_ZONESETTINGS + s) * ka_.zone_stride + zn] -
-                ka_.zone[((long long)im * N_ZONESETTINGS + s) * ka_.zone_stride + zn]) * (real_t)0.5;
+        real_t v = (ka_.zone[((long long)ip * N_ZONESETTINGS + s) * ka_.zone_stride + zn] -
+                    ka_.zone[((long long)im * N_ZONESETTINGS + s) * ka_.zone_stride + zn]) * (real_t)0.5;
+#ifdef TCLB_AD
+        ad_seed_zone(v, s, 1);
+#endif
+        return v;
     }
-    TCLB_HD real_t load_field(int fi, int dx, int dy, int dz) const {
+    TCLB_HD real_t load_field_plain(int fi, int dx, int dy, int dz) const {
         int xx = tclbrt::wrapx(n_x, dx, ka_.nx);
         long long i = ((long long)(n_z + dz + GZ) * ka_.NY + (n_y + dy + GY)) * ka_.nx + xx;
         return TCLB_LD(ka_.in[fi * ka_.fstride + i], field_shift(fi));
     }
+#if TCLB_AUTOSYM > 0
+    // option autosym (reference SymmetryAccess, src/LatticeAccess.inc.cpp.Rt:376-447): a read that crosses a mirror plane
+    // of this node (node types Symmetry<X|Y|Z>_<plus|minus>) is redirected to the mirror partner of the field at the
+    // reflected offset; z is resolved first, then y, then x, as in the reference's load_ -> loadY_ -> loadX_ chain
+    TCLB_HD real_t load_field(int fi, int dx, int dy, int dz) const {
+        int d[3] = {dx, dy, dz};
+        real_t sg = 1;
+#pragma unroll
+        for (int ax = 2; ax >= 0; ax--) {
+            const unsigned grp = (unsigned)n_type & t_sym_mask(ax);
+            if (d[ax] > 0 && grp != 0 && grp == t_sym_plus(ax)) { d[ax] = TCLB_AUTOSYM_SHIFT - d[ax]; sg *= t_sym_sign(fi, ax); fi = t_sym_field(fi, ax); }
+            else if (d[ax] < 0 && grp != 0 && grp == t_sym_minus(ax)) { d[ax] = -TCLB_AUTOSYM_SHIFT - d[ax]; sg *= t_sym_sign(fi, ax); fi = t_sym_field(fi, ax); }
+        }
+        return sg * load_field_plain(fi, d[0], d[1], d[2]);
+    }
+#else
+    TCLB_HD real_t load_field(int fi, int dx, int dy, int dz) const { return load_field_plain(fi, dx, dy, dz); }
+#endif
     TCLB_HD real_t load_field(int fi, int dx, int dy) const { return load_field(fi, dx, dy, 0); }
-    TCLB_HD ParticleRange<ParticleS> SyncParticleIterator(real_t x, real_t y, real_t z) const {
-        return ParticleRange<ParticleS>{ka_.particles, ka_.n_particles, x, y, z};
+    template <class P> TCLB_HD ParticleRange<P> particle_range(real_t x, real_t y, real_t z) const {
+        return ParticleRange<P>(ka_.particles, ka_.n_particles, x, y, z, ka_.pgrid, ka_.pg_n, ka_.pg_depth, ka_.pg_origin, ka_.pg_inv_delta);
     }
-    TCLB_HD ParticleRange<ParticleI> ParticleIterator(real_t x, real_t y, real_t z) const {
-        return ParticleRange<ParticleI>{ka_.particles, ka_.n_particles, x, y, z};
-    }
+    TCLB_HD ParticleRange<ParticleS> SyncParticleIterator(real_t x, real_t y, real_t z) const { return particle_range<ParticleS>(x, y, z); }
+    TCLB_HD ParticleRange<ParticleI> ParticleIterator(real_t x, real_t y, real_t z) const { return particle_range<ParticleI>(x, y, z); }
     TCLB_HD uint16_t getQ(int d) const {
         return ka_.cuts ? ka_.cuts[(long long)d * ((long long)ka_.nx * ka_.NY * ka_.NZ) + n_idx] : (uint16_t)NO_CUT;
     }
@@ -487,9 +664,13 @@ struct Node {
 // ---------------------------------------------------------------- model physics ----
 #ifdef TCLB_DOUBLE
 """)
-    A(m.code)
+    # older iterator form of some shipped models: `for (ParticleIterator p(X,Y,Z); p; ++p)` declares the iterator as an object
+    # (also the Tree.../Full... spellings of earlier container generations)
+    code = re.sub(r"\bSync(?:Full)?ParticleIterator\s+(\w+)\s*\(", r"OldParticleIterator<ParticleS, Node<GMODE> > \1(*this, ", m.code)
+    code = re.sub(r"(?<![<\w])(?:Tree|Full)?ParticleIterator\s+(\w+)\s*\(", r"OldParticleIterator<ParticleI, Node<GMODE> > \1(*this, ", code)
+    A(code)
     A("#else")
-    A(to_single_precision(m.code))
+    A(to_single_precision(code))
     A("#endif")
     A("// ---------------------------------------------------------------- end of model physics ----")
     # quantity accessors dispatch
@@ -548,6 +729,7 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
                 A(f"    n.{d.name} = TCLB_LD(a.ldp[{di}][{_xidx(d.dx)}], {shift_of[d.field]!r});")
             elif d.default is not None:
                 A(f"    n.{d.name} = (real_t){d.default!r};")
+        A(_autosym_resolve(m, s, fidx))
         A("}")
         A(f"template <int GMODE> TCLB_HD void store_stage_{si}(Node<GMODE> &n, const KArgs &a, int x, int y, int z, bool border) {{")
         for f in m.fields:
@@ -578,7 +760,7 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
                 edges += [(k, -j, di) for j in range(1, d.dx + 1)]
             elif d.dx < 0:
                 edges += [(k, 128 + j, di) for j in range(0, -d.dx)]
-        ok = bool(ld) and all(abs(d.dx) <= 2 for _, d in ld)
+        ok = bool(ld) and all(abs(d.dx) <= 2 for _, d in ld) and not int(getattr(m, "autosym", 0) or 0)
         ring_ok.append(ok)
         A(f"constexpr int RING_ROWS_{si} = {len(ld) if ok else 0}, RING_EDGES_{si} = {len(edges) if ok else 0};")
         A(f"constexpr int RING_BYTES_{si} = RING_ROWS_{si} * RING_ROW + TCLB_TILE_X * (int)sizeof(flag_t);")
@@ -591,15 +773,15 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
                 if not d.load.get(s_.name) and d.default is not None:
                     A(f"    n.{d.name} = (real_t){d.default!r};")
         A("}")
-        # rows: issued by one thread; `row0` = index of the tile's first node in a field
-        A(f"TCLB_D void ring_issue_rows_{si}(const KArgs &a, unsigned char *sb, void *bar, long long row0) {{")
+        # rows: lane 0 of every warp issues its share (row k belongs to warp k % 4), so no warp is held up by the whole
+        # list; warp 0 also announces the byte count.  `row0` = index of the tile's first node in a field
+        A(f"TCLB_D void ring_issue_rows_{si}(const KArgs &a, unsigned char *sb, void *bar, long long row0, int wid) {{")
         if ok:
-            A(f"    tclbrt::mbar_arrive_expect_tx(bar, (unsigned)(RING_ROWS_{si} * TCLB_TILE_X * (int)sizeof(storage_t) + TCLB_TILE_X * (int)sizeof(flag_t)));")
+            A(f"    if (wid == 0) tclbrt::mbar_arrive_expect_tx(bar, (unsigned)(RING_ROWS_{si} * TCLB_TILE_X * (int)sizeof(storage_t) + TCLB_TILE_X * (int)sizeof(flag_t)));")
             for k, (di, d) in enumerate(ld):
-                A(f"    tclbrt::bulk_g2s(sb + {k} * RING_ROW + 16, a.ldp[{di}] + row0, TCLB_TILE_X * (unsigned)sizeof(storage_t), bar);")
-            A(f"    tclbrt::bulk_g2s(sb + RING_ROWS_{si} * RING_ROW, a.flags + row0, TCLB_TILE_X * (unsigned)sizeof(flag_t), bar);")
+                A(f"    if (wid == {k % 4}) tclbrt::bulk_g2s(sb + {k} * RING_ROW + 16, a.ldp[{di}] + row0, TCLB_TILE_X * (unsigned)sizeof(storage_t), bar);")
+            A(f"    if (wid == {len(ld) % 4}) tclbrt::bulk_g2s(sb + RING_ROWS_{si} * RING_ROW, a.flags + row0, TCLB_TILE_X * (unsigned)sizeof(flag_t), bar);")
         A("}")
-        # edge elements: spread over the lanes of the issuing warp
         if ok and edges:
             # one packed word per edge element in constant memory: row | field << 8 | (position + 8) << 16 | (dy + 2) << 24 |
             # (dz + 2) << 27 (the source pointer is rebuilt from these: indexing the kernel parameter array with a lane
@@ -621,9 +803,9 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     for si in range(len(m.stages)):
         A(f"    if (S == {si}) load_stage_ring_{si}(n, sb, t);")
     A("}")
-    A("template <int S> TCLB_D void ring_issue_rows(const KArgs &a, unsigned char *sb, void *bar, long long row0) {")
+    A("template <int S> TCLB_D void ring_issue_rows(const KArgs &a, unsigned char *sb, void *bar, long long row0, int wid) {")
     for si in range(len(m.stages)):
-        A(f"    if (S == {si}) ring_issue_rows_{si}(a, sb, bar, row0);")
+        A(f"    if (S == {si}) ring_issue_rows_{si}(a, sb, bar, row0, wid);")
     A("}")
     A("template <int S> TCLB_D void ring_issue_edges(const KArgs &a, unsigned char *sb, int lane, long long row0, int x0) {")
     for si in range(len(m.stages)):
@@ -635,6 +817,13 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     A("template <int GMODE> TCLB_HD void load_all(Node<GMODE> &n, const KArgs &a, int x, int i0, int im, int ip) {")
     for di, d in enumerate(m.densities):
         A(f"    n.{d.name} = TCLB_LD(a.ldp[{di}][{_xidx(d.dx)}], {shift_of[d.field]!r});")
+    class _AllStage:       # quantities see every density, resolved at symmetry nodes like a stage that loads them all
+        name = "\0all"
+    for d in m.densities:
+        d.load["\0all"] = True
+    A(_autosym_resolve(m, _AllStage, fidx))
+    for d in m.densities:
+        d.load.pop("\0all", None)
     A("}")
     A("template <int S, int GMODE> TCLB_HD void load_stage(Node<GMODE> &n, const KArgs &a, int x, int i0, int im, int ip) {")
     for si in range(len(m.stages)):
@@ -706,6 +895,12 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     A("    switch (stage) {")
     for si in range(len(m.stages)):
         A(f"    case {si}: return run_adjoint_settings<{si}>(a, L, (const base_t *)adj_out, which, n, grad);")
+    A('    default: set_error("bad stage"); return -1;\n    }\n}')
+    A('extern "C" int tclb_model_adjoint_zsettings(int stage, const tclb_launch_t *L, const void *adj_out, const int *zs, const int *zone, const int *dt, int n, double *grad) {')
+    A("    KArgs a; int bx, by; fill_args(a, L, bx, by);")
+    A("    switch (stage) {")
+    for si in range(len(m.stages)):
+        A(f"    case {si}: return run_adjoint_zsettings<{si}>(a, L, (const base_t *)adj_out, zs, zone, dt, n, grad);")
     A('    default: set_error("bad stage"); return -1;\n    }\n}')
     A('extern "C" const char *tclb_model_adjoint_error(void) { return g_error; }')
     A(f'extern "C" int tclb_model_adjoint_info(int *real_size, int *dirs, int *n_fields) {{ *real_size = (int)sizeof(base_t); *dirs = TCLB_AD_DIRS; *n_fields = N_FIELDS; return TCLB_ABI_VERSION; }}')
@@ -818,7 +1013,8 @@ const tclb_model_t t_model = {{
     {len(m.stages)}, t_stages, {len(m.actions)}, t_actions, {len(m.options)}, t_options,
     GY, GZ,
     run_stage_impl, get_quantity_impl, color_impl, kernel_info_impl, last_error_impl,
-    (int)sizeof(storage_t), TCLB_STORAGE_SHIFTED, TCLB_STORAGE_NAME, t_field_shift
+    (int)sizeof(storage_t), TCLB_STORAGE_SHIFTED, TCLB_STORAGE_NAME, t_field_shift,
+    (double)PART_MAR_VALUE
 }};
 }}  // namespace
 extern "C" const tclb_model_t *tclb_get_model(void) {{ return &t_model; }}

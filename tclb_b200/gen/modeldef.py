@@ -46,6 +46,7 @@ class Density:
     adjoint: bool = False
     default: Optional[float] = None
     load: Dict[str, bool] = field(default_factory=dict)      # stage -> loaded?
+    sym: List[str] = field(default_factory=lambda: ["", "", ""])   # mirror partner per axis (autosym), "-name" = with sign
 
 
 @dataclass
@@ -67,6 +68,7 @@ class Field:
     non_mandatory: bool = False
     save: Dict[str, bool] = field(default_factory=dict)      # stage -> saved?
     read: Dict[str, Optional[bool]] = field(default_factory=dict)
+    sym: List[str] = field(default_factory=lambda: ["", "", ""])   # mirror partner per axis (autosym), "-name" = with sign
 
     @property
     def simple_access(self) -> bool:
@@ -215,10 +217,15 @@ class ModelDef:
                         comment=comments[i] or nm, group=grp, parameter=bool(parameter),
                         average=bool(average), adjoint=bool(adjoint),
                         default=None if default is None else float(default))
+            if sym is not None:
+                sv = [str(x) for x in _aslist(sym)]
+                if len(sv) != 3:
+                    raise ModelError("sym provided to AddDensity have to be a vector of length 3")
+                d.sym = sv
             self.densities.append(d)
             self.AddField(name=d.field, dx=-d.dx, dy=-d.dy, dz=-d.dz, comment=d.comment,
                           adjoint=adjoint, group=grp, parameter=parameter, average=average,
-                          shift=shifts[i], **kw)
+                          shift=shifts[i], sym=sym, **kw)
 
     def AddField(self, name, stencil2d=None, stencil3d=None, dx=0, dy=0, dz=0, comment="",
                  adjoint=False, group=None, parameter=False, average=False, sym=None, shift=None,
@@ -241,6 +248,10 @@ class ModelDef:
                       shift=None if shift in (None, 0) else float(shift),
                       optimise_for_static_access=bool(optimise_for_static_access),
                       non_mandatory=bool(non_mandatory))
+            if sym is not None:
+                sv = [str(x) for x in _aslist(sym)]
+                if len(sv) == 3:
+                    f.sym = sv
             old = self.field(nm, missing_ok=True)
             if old is not None:
                 old.minx = min(old.minx, f.minx); old.maxx = max(old.maxx, f.maxx)
@@ -375,6 +386,7 @@ class ModelDef:
             self.objectives.setdefault(g.name, g.name)
         if self.description is None:
             self.AddDescription(self.name)
+        self._autosym()
         # default actions / stages
         if not any(a.name == "Iteration" for a in self.actions):
             self.AddAction("Iteration", ["BaseIteration"])
@@ -431,6 +443,75 @@ class ModelDef:
                 s.derived, s.equation = None, None
         self.finalized = True
         return self
+
+    def _autosym(self):
+        """Option autosym (reference src/conf.R:373-457): every density gets its mirror partner per axis (same group,
+        mirrored velocity; `sym=` of AddDensity/AddField overrides, "-name" mirrors with a sign), the reach of every field
+        is closed under the mirror maps (x -> -x for autosym=1, a plane through the nodes; x -> 1-x / -1-x for autosym=2,
+        a plane on the cell edge), and the node types Symmetry{X,Y,Z}_{plus,minus} (SymmetryEdge... for 2) are added."""
+        mode = self.options.get("autosym", 0)
+        mode = int(mode) if not isinstance(mode, bool) else (1 if mode else 0)
+        self.autosym = mode
+        if mode <= 0:
+            return
+        if mode not in (1, 2):
+            raise ModelError("unknown autosym value")
+        mirrors = [(-1, 1, 1), (1, -1, 1), (1, 1, -1)]
+        by_field = {f.name: f for f in self.fields}
+        for g in dict.fromkeys(d.group for d in self.densities):
+            D = [d for d in self.densities if d.group == g]
+            for d in D:
+                v = (d.dx, d.dy, d.dz)
+                for ax in range(3):
+                    if d.sym[ax] != "":
+                        continue
+                    if v == (0, 0, 0):
+                        partner = d
+                    else:
+                        sv = tuple(a * b for a, b in zip(v, mirrors[ax]))
+                        found = [o for o in D if (o.dx, o.dy, o.dz) == sv]
+                        if len(found) == 0:
+                            raise ModelError(f"Could not find symmetry for density {d.name}")
+                        if len(found) > 1:
+                            raise ModelError(f"Too many symmetries for density {d.name}")
+                        partner = found[0]
+                    d.sym[ax] = partner.name
+                    if by_field[d.field].sym[ax] == "":
+                        by_field[d.field].sym[ax] = partner.field
+        for f in self.fields:
+            for ax in range(3):
+                if f.sym[ax] == "":
+                    f.sym[ax] = f.name
+        shift = 0 if mode == 1 else 1
+        self.autosym_shift = shift
+        self.autosym_name = "Symmetry" if mode == 1 else "SymmetryEdge"
+        dirs = {f.name: {(x, y, z) for x in range(f.minx, f.maxx + 1) for y in range(f.miny, f.maxy + 1) for z in range(f.minz, f.maxz + 1)}
+                for f in self.fields}
+        while True:
+            before = {k: set(v) for k, v in dirs.items()}
+            for f in self.fields:
+                d = dirs[f.name]
+                for ax in range(3):
+                    nfn = f.sym[ax].lstrip("-")
+                    add = set()
+                    for p in d:
+                        if p[ax] < 0:
+                            q = list(p); q[ax] = -p[ax] - shift; add.add(tuple(q))
+                        elif p[ax] > 0:
+                            q = list(p); q[ax] = -p[ax] + shift; add.add(tuple(q))
+                    dirs[nfn] = dirs[nfn] | add
+            if dirs == before:
+                break
+        for f in self.fields:
+            pts = dirs[f.name]
+            f.minx, f.maxx = min(p[0] for p in pts), max(p[0] for p in pts)
+            f.miny, f.maxy = min(p[1] for p in pts), max(p[1] for p in pts)
+            f.minz, f.maxz = min(p[2] for p in pts), max(p[2] for p in pts)
+        nm = self.autosym_name
+        self.AddNodeType(nm + "X_plus", "SYMX"); self.AddNodeType(nm + "X_minus", "SYMX")
+        self.AddNodeType(nm + "Y_plus", "SYMY"); self.AddNodeType(nm + "Y_minus", "SYMY")
+        if not all(f.minz == 0 and f.maxz == 0 for f in self.fields):
+            self.AddNodeType(nm + "Z_plus", "SYMZ"); self.AddNodeType(nm + "Z_minus", "SYMZ")
 
     def _check_actions(self):
         snames = [s.name for s in self.stages]

@@ -317,6 +317,7 @@ def install(I):
     G.set("readLines", _readlines)
     G.set("nlevels", lambda I, a, k: vec(0))
     G.set("rows", lambda I, a, k: _rows(a[0]))
+    G.set(".GlobalEnv", vec("<globalenv>"))      # assign(..., envir=.GlobalEnv): assign() always writes the global scope here
     G.set("pi", vec(math.pi))
     G.set("T", vec(True))       # ordinary variables in R: models do assign to F and T
     G.set("F", vec(False))

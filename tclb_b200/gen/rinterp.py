@@ -521,6 +521,8 @@ class Interp:
                 return Poly.const(float(v)) if not isinstance(v, str) else Poly.sym(v)
             return PVec([float(t) for t in x.tolist()])
         A, B = lift(a), lift(b)
+        if op == "%%":          # older polyAlgebra spelling of the symbolic matrix product
+            op = "%*%"
         if op == "%*%":
             if isinstance(A, PVec) and isinstance(B, np.ndarray):
                 return A @ _num(B).astype(float)

@@ -177,14 +177,35 @@ def install_feq(I, env):
             r[kk] = v
         return r
 
+    def wmrt_mat(I_, a, k):
+        """WMRT_mat(U) (src/lib/feq.R:90-113): the polynomial moment matrix recombined so that the high-order equilibrium
+        becomes "triangular" in the monomials of (rho, J): M %*% solve(R), R = unit-diagonal upper factor of the QR
+        decomposition of the table of coefficients of the equilibrium moments."""
+        U = _mat(a[0]).astype(int)
+        try:
+            eq = lbmlib.mrt_eq(U, rho=Poly.sym("rho"), J=PVec(["Jx", "Jy", "Jz"]), sigma2=1.0 / 3.0, order=300, orthogonal=False, mat=None)
+        except ValueError as e:
+            raise RError(str(e))
+        M = np.asarray(eq.mat, dtype=float)
+        monos = []
+        for p in eq.Req:
+            for mono in p.t:
+                if mono not in monos:
+                    monos.append(mono)
+        n = len(eq.Req)
+        A = np.array([[float(p.t.get(mono, 0.0)) for p in eq.Req] for mono in monos], dtype=float)
+        R = np.eye(n)
+        r = np.linalg.qr(A, mode="r")
+        R[:r.shape[0], :] = r[:n, :]
+        R = R / np.diag(R)[:, None]
+        return M @ np.linalg.inv(R)
+
+    env.set("WMRT_mat", wmrt_mat)
     env.set("MRT_polyMatrix", mrt_polymatrix)
     env.set("MRT_integerOrtogonal", lambda I_, a, k: lbmlib.integer_orthogonalise(_mat(a[0])))
     env.set("MRT_eq", mrt_eq)
     env.set("MRT_feq", lambda I_, a, k: mrt_eq(I_, a, k)["feq"])
 
-    def wmrt(I_, a, k):
-        raise RError("WMRT_mat is not available in this front-end")
-    env.set("WMRT_mat", wmrt)
     return NULL
 
 
@@ -449,7 +470,47 @@ def install_utils(I, env):
     return NULL
 
 
+# ---------------------------------------------------------------------------------------------- cumulant.R
+def install_cumulant(I, env):
+    """FCT_eq(I, M, K) (src/lib/cumulant.R:7-44): moments expressed through cumulants by the recursion
+    m_p = sum over subsets S of p \\ {s} of m_S * k_(p \\ S), for every multi-index row of I (after the first); of the
+    len(p) equivalent forms (one per choice of the distinguished element s) the one with the fewest factors is kept."""
+    import itertools
+    axes = ["X", "Y", "Z"]
+
+    def ord_(p):                      # 1-based position of a multiset of axes in the 3x3x3 tables
+        return sum(p.count(v) * 3 ** k for k, v in enumerate(axes)) + 1
+
+    def fct_eq(I_, a, k):
+        g = _args(["I", "M", "K"], a, k)
+        idx = _mat(g["I"]).astype(int)
+        Mv, Kv = _pvec(g["M"]), _pvec(g["K"])
+        out = Mv.copy()
+        for r in range(1, idx.shape[0]):
+            p = [axes[c] for c in range(idx.shape[1]) for _ in range(int(idx[r, c]))]
+            n = len(p)
+            subsets = [tuple(bool((j >> b) & 1) ^ True for b in range(n)) for j in range(2 ** n)]   # expand.grid(c(TRUE,FALSE)...): first column fastest
+            cands = []
+            for s_ in range(n):
+                tot = Poly()
+                for sel in subsets:
+                    if sel[s_]:
+                        continue
+                    inside = [p[i] for i in range(n) if sel[i]]
+                    outside = [p[i] for i in range(n) if not sel[i]]
+                    tot = tot + Mv[ord_(inside) - 1] * Kv[ord_(outside) - 1]
+                cands.append(tot)
+            cost = [len(to_c(c).split("*")) for c in cands]
+            out[ord_(p) - 1] = cands[int(np.argmin(cost))]
+        return out
+
+    env.set("FCT_eq", fct_eq)
+    env.set("all.subsets", lambda I_, a, k: np.array([[bool((j >> b) & 1) ^ True for b in range(int(scalar(a[0])))] for j in range(2 ** int(scalar(a[0])))], dtype=bool))
+    return NULL
+
+
 HOOKS = {
+    "lib/cumulant.R": install_cumulant,
     "lib/lattice.R": install_lattice,
     "lib/feq.R": install_feq,
     "lib/boundary.R": install_boundary,

@@ -17,13 +17,15 @@ from ..gen.modeldef import ModelDef
 from ..gen.poly import PV, Poly, PVec, c_assign, to_c
 
 NAME = "d2q9"
-OPTIONS = ["bc"]          # the reference's OPT="bc*autosym"; autosym is a memory-layout variant
-VARIANTS = [dict(), dict(bc=True)]
+OPTIONS = ["bc", "autosym", "autosym2"]      # the reference's OPT="bc*autosym" (variants autosym = 1, autosym2 = 2: src/models.R:52-57)
+VARIANTS = [dict(), dict(bc=True), dict(autosym=True), dict(autosym2=True), dict(bc=True, autosym=True), dict(bc=True, autosym2=True)]
 
 
 def build(options=None) -> ModelDef:
     opt = dict(bc=False)
     opt.update(options or {})
+    sym = 2 if opt.pop("autosym2", False) else (1 if opt.get("autosym") else 0)
+    opt["autosym"] = sym
     m = ModelDef(NAME, opt)
     U = d2q9_velocities()
     w = [4 / 9] + [1 / 9] * 4 + [1 / 36] * 4

@@ -178,6 +178,11 @@ CudaDeviceFunction float2 Color() {
     A("\tJx += rho*ForceX;\n\tJy += rho*ForceY;\n\tJz += rho*ForceZ;")
     A(c_assign(Rs[selR], (Rs + Req)[selR]))
     A(sym_populations(Rs, np.diag(1.0 / norm) @ Mm, U, f))
+    # the reference divides ALL moments by the squared norms of the MRT rows before it forms the velocity for the
+    # Globals (`C(R, Mw, eq="/=")`, models/flow/d3q19/Dynamics.c.Rt:263-265), so VOLrho, VOLp*, VOLv*, the slice sums and
+    # MaxV are sums of those scaled moments; a log written by this model has to carry the same numbers
+    A("\t" + " ".join(f"{to_c(Rs[i])} = {to_c(Rs[i])} * {1.0 / float(norm[i])!r};" for i in range(19)
+                     if to_c(Rs[i]) in ("rho", "Jx", "Jy", "Jz")))
     A("""	real_t ux, uy, uz;
 	ux = Jx / rho;
 	uy = Jy / rho;

@@ -20,7 +20,9 @@ _RED_FN = C.CFUNCTYPE(None, C.c_void_p, C.POINTER(C.c_double), C.c_int, C.c_int)
 
 class DistDomain:
     def __init__(self, model: Model, shape, rank: int = 0, world: int = 1, device: int = 0, backend: str = "cuda",
-                 direct: bool = True, init_pg: bool = True):
+                 direct: bool = True, init_pg: bool = True, domain: Optional[Domain] = None):
+        """`domain`: wire an existing Domain (created with nranks=world, local_ranks=[rank]) instead of making one - how a
+        case-file Solver joins a multi-process run (tclb_b200.run under torchrun)."""
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -34,11 +36,12 @@ class DistDomain:
             if backend == "cuda":
                 kw["device_id"] = torch.device("cuda", device)
             dist.init_process_group("nccl" if backend == "cuda" else "gloo", rank=rank, world_size=world, **kw)
-        self.domain = Domain(model, shape, backend, nranks=world, local_ranks=[rank], devices=[device])
+        self.domain = domain if domain is not None else Domain(model, shape, backend, nranks=world, local_ranks=[rank], devices=[device])
         self._cb = []
         if world > 1:
             if direct and backend == "cuda":
                 self._wire_ipc()
+                self._wire_hooks(exchange_too=False)     # handler collectives (Failcheck ...) still need the reduction
             else:
                 self.domain.set_halo_mode(False)
                 self._wire_hooks()
@@ -62,14 +65,16 @@ class DistDomain:
         self.barrier()
 
     # ---- baseline: NCCL / gloo ----
-    def _wire_hooks(self):
+    def _wire_hooks(self, exchange_too: bool = True):
         torch, dist = self.torch, self.dist
         d = self.domain
         dev = torch.device("cuda", self.device) if self.backend == "cuda" else torch.device("cpu")
         nf = len(self.model.fields)
         gy, gz = self.model.gy, self.model.gz
         x0, y0, z0, nx, ny, nz = d.boxes[self.rank]
-        dtype = torch.float64 if self.model.precision == "double" else torch.float32
+        # the snapshot holds STORAGE values (float16 for *_half builds), not the arithmetic type
+        dtype = {2: torch.float16, 4: torch.float32, 8: torch.float64}[int(self.model.d.storage_size)]
+        esize = int(self.model.d.storage_size)
 
         def snapshot_tensor(snap):
             ptr, shp, _, _, _ = d.snapshot_info(self.rank, snap)
@@ -77,7 +82,7 @@ class DistDomain:
             if self.backend == "cuda":
                 from ..utils.interop import tensor_from_ptr
                 return tensor_from_ptr(ptr, shp, dtype, self.device)
-            buf = (C.c_char * (n * (8 if dtype == torch.float64 else 4))).from_address(ptr)
+            buf = (C.c_char * (n * esize)).from_address(ptr)
             return torch.frombuffer(buf, dtype=dtype).view(*shp)
 
         divy, divz = d.divy, d.divz
@@ -128,8 +133,8 @@ class DistDomain:
             a[:] = tt.cpu().numpy()
 
         ex, red = _EX_FN(exchange), _RED_FN(reduce)
-        self._cb = [ex, red]
-        _check(d.lib.tclb_domain_set_hooks(d.h, C.cast(ex, C.c_void_p), C.cast(red, C.c_void_p), None))
+        self._cb += [ex, red]
+        _check(d.lib.tclb_domain_set_hooks(d.h, C.cast(ex, C.c_void_p) if exchange_too else None, C.cast(red, C.c_void_p), None))
 
     # ---- helpers ----
     def set_local_flags(self, flags_local: np.ndarray):

@@ -154,6 +154,7 @@ def core():
         "tclb_domain_use_graphs": [C.c_void_p, C.c_int],
         "tclb_domain_graph_iterations": [C.c_void_p],
         "tclb_domain_save_pri": [C.c_void_p, C.c_int, C.c_char_p],
+        "tclb_domain_pri_blocks": [C.c_void_p, C.c_int, C.POINTER(C.c_longlong)],
         "tclb_domain_load_pri": [C.c_void_p, C.c_int, C.c_char_p],
         "tclb_domain_snapshot_ptr": [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)],
         "tclb_domain_flags_ptr": [C.c_void_p, C.c_int],
@@ -409,6 +410,12 @@ class Domain:
         out = np.zeros((by, bx, 4), dtype=np.uint8)
         _check(self.lib.tclb_domain_color(self.h, rank, zplane, float(scale), out.ctypes.data))
         return out
+
+    def pri_blocks(self, rank: int = 0):
+        """elements of the 27 margin blocks of rank's checkpoint image (block1 .. block27 of the reference)"""
+        out = (C.c_longlong * 27)()
+        _check(self.lib.tclb_domain_pri_blocks(self.h, rank, out))
+        return list(out)
 
     def save_pri(self, rank: int, path: str):
         _check(self.lib.tclb_domain_save_pri(self.h, rank, str(path).encode()))

@@ -52,3 +52,42 @@ def test_two_process_gloo_matches_single(tmp_path, built):
         x0, y0, z0, nx, ny, nz = np.load(tmp_path / f"box_{rk}.npy")
         u[z0:z0 + nz, y0:y0 + ny, x0:x0 + nx] = np.load(tmp_path / f"u_{rk}.npy")
     assert np.array_equal(u, ref["U"])
+
+
+def test_case_file_on_two_processes_matches_golden_karman(tmp_path, built):
+    """The reference's karman case run as a CASE FILE by two processes (torch.distributed/gloo, one subdomain each,
+    `python -m tclb_b200.run` under torchrun): rank 0 writes the Log (golden values of tests/external/d2q9/karman_p2.test)
+    and the .pvti index, every rank its .vti piece; a checkpoint written on the way restarts to the same result."""
+    import csv
+    from tclb_b200 import build
+    build.build_model_lib("d2q9", "double")
+    from golden_karman import KARMAN_IT1000, KARMAN_XML
+    xml = KARMAN_XML.replace("<Solve", '<VTK Iterations="1000"/>\n<SaveCheckpoint Iterations="500" keep="all"/>\n<Solve', 1)
+    (tmp_path / "karman.xml").write_text(xml)
+    env = dict(os.environ, OMP_NUM_THREADS="2", PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+
+    def launch(case, port):
+        r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                            "--master-port", str(port), "-m", "tclb_b200.run", "--cpu", "--precision", "double", "d2q9", case],
+                           cwd=tmp_path, capture_output=True, text=True, timeout=1200, env=env)
+        assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+    launch("karman.xml", 29621)
+    out = tmp_path / "output"
+    rows = list(csv.reader(open(out / "karman_Log_P00_00000000.csv")))
+    last = dict(zip(rows[0], rows[-1]))
+    for k, v in KARMAN_IT1000.items():
+        assert abs(float(last[k]) - v) <= 1e-9 * abs(v), (k, last[k], v)
+    names = sorted(os.listdir(out))
+    assert "karman_VTK_P00_00001000.pvti" in names and "karman_VTK_P00_00001000.vti" in names and "karman_VTK_P01_00001000.vti" in names
+    assert b"karman_VTK_P01_00001000.vti" in open(out / "karman_VTK_P00_00001000.pvti", "rb").read()
+    # restart from the checkpoint of iteration 500 (per-rank .pri files + restart XML written by rank 0)
+    assert "karman_checkpoint_00000500_0.pri" in names and "karman_checkpoint_00000500_1.pri" in names and "karman_restart_00000500.xml" in names
+    launch(os.path.join("output", "karman_restart_00000500.xml"), 29622)
+    logs = [f for f in os.listdir(out) if f.startswith("karman_restart_00000500_Log")]
+    assert logs, sorted(os.listdir(out))
+    # the iteration counter is not part of a checkpoint (like the reference): 500 iterations after the restart = 1000 in all
+    rows2 = list(csv.reader(open(out / logs[0])))
+    at500 = [dict(zip(rows2[0], r)) for r in rows2[1:] if int(float(r[0])) == 500][0]
+    for k, v in KARMAN_IT1000.items():
+        assert abs(float(at500[k]) - v) <= 1e-9 * abs(v), (k, at500[k], v)
