@@ -21,7 +21,12 @@ class Adjoint {
     void record(int n);          // n primal iterations with the input of each kept on the tape; Objective accumulated
     void reverse();              // sweep the tape backwards; afterwards adjoint() is dObjective/d(state at the start)
     void drop_tape();
-    size_t tape_length() const { return tape_.size(); }
+    size_t tape_length() const { return (size_t)tape_count_; }     // iterations recorded
+    size_t tape_frames() const { return tape_.size(); }            // states actually held
+    // bound the number of stored states (0 = keep every iteration's input): the forward run then keeps checkpoints at a
+    // stride that doubles when the budget fills up, and reverse() recomputes the iterations in between (bisection when a
+    // gap is longer than the free slots).  Also TCLB_TAPE_FRAMES=<n>.
+    void set_tape_frames(int n);
     // ---- steady ----
     void steady(int n);          // n adjoint iterations around the current state (input of the next primal iteration)
     // ---- access ----
@@ -59,25 +64,42 @@ class Adjoint {
     void settings_pass(const tclb_launch_t &L, const void *adj_out);
     typedef int (*stage_fn)(int, const tclb_launch_t *, const void *, void *);
     typedef const char *(*err_fn)(void);
-    struct Frame { void *data; bool on_device; int iter; };
+    // one stored state of the whole lattice: per subdomain the current snapshot (+ the other one for multi-stage actions)
+    struct Frame { std::vector<void *> data, pre; bool on_device = false; int iter = 0; long index = 0; };
+    // per subdomain: two adjoint buffers (snapshot layout in real_t), and for multi-stage actions a scratch adjoint, the
+    // adjoint left over for the previous state, and the state before every later stage
+    struct Sub { Lattice *lat = nullptr; void *adj[2] = {nullptr, nullptr}; void *tmp = nullptr, *resid = nullptr; std::vector<void *> inter; size_t bytes = 0; };
     Domain *dom_;
     Lattice *lat_;
+    std::vector<Sub> subs_;
+    std::vector<int> stages_;            // stages of the Iteration action
     void *lib_ = nullptr;
     stage_fn fn_ = nullptr;
     err_fn err_ = nullptr;
     int rs_ = 8, action_ = -1, stage_ = -1;
-    void *adj_[2] = {nullptr, nullptr};
     int cur_ = 0;
-    size_t bytes_ = 0;           // one adjoint buffer = n_fields * plane_elems * real_size
+    size_t bytes_ = 0;
     std::vector<Frame> tape_;
+    long tape_count_ = 0, stride_ = 1;   // iterations recorded since the tape was empty; spacing of the kept checkpoints
+    int max_frames_ = 0;                 // 0: keep every input state
     size_t dev_tape_bytes_ = 0, dev_tape_cap_ = 0;
-    void step(const void *primal_in, int iter);   // adj_[cur^1] = J^T adj_[cur] + dObj; then swap
-    std::vector<void *> pool_dev_, pool_host_;    // recycled tape frames
-    void *frame_get(bool device);
-    void frame_put(void *p, bool device);
-    void *alloc(size_t bytes, bool device) const;
+    std::vector<std::pair<void *, bool>> pool_;      // recycled frame buffers (pointer, on device)
+    std::vector<size_t> pool_bytes_;
+    std::vector<int> pool_dev_id_;
+    Frame grab_frame(bool with_pre);
+    void free_frame(Frame &f);
+    void restore_frame(const Frame &f);
+    void *frame_get(const Sub &s, bool device);
+    void frame_put(void *p, bool device, size_t bytes);
+    void copy_snap(const Sub &s, void *dst, const void *src, bool dst_dev, bool src_dev) const;
+    void step(const std::vector<const void *> &in, const std::vector<const void *> &pre, int iter);
+    void reverse_segment(const Frame &f, long len, int slots);
+    void launch_adjoint(Sub &s, int stage, const void *primal_in, int iter, const void *adj_out, void *adj_in);
+    void zero_fields(Sub &s, void *buf, const unsigned char *which);
+    void fold(int which_buf);
+    void *alloc(const Sub &s, size_t bytes, bool device) const;
     void release(void *p, bool device) const;
-    void fill_zero(void *p) const;
+    void fill_zero(const Sub &s, void *p) const;
 };
 
 }  // namespace tclb

@@ -328,6 +328,8 @@ void tclb_adjoint_destroy(tclb_adjoint_h *a) { if (a) { delete a->a; delete a; }
 int tclb_adjoint_record(tclb_adjoint_h *a, int n) { GUARD_BEGIN a->a->record(n); GUARD_END_INT }
 int tclb_adjoint_reverse(tclb_adjoint_h *a) { GUARD_BEGIN a->a->reverse(); GUARD_END_INT }
 int tclb_adjoint_steady(tclb_adjoint_h *a, int n) { GUARD_BEGIN a->a->steady(n); GUARD_END_INT }
+int tclb_adjoint_set_tape_frames(tclb_adjoint_h *a, int n) { GUARD_BEGIN a->a->set_tape_frames(n); GUARD_END_INT }
+int tclb_adjoint_tape_frames(tclb_adjoint_h *a) { return (int)a->a->tape_frames(); }
 int tclb_adjoint_zero(tclb_adjoint_h *a) { GUARD_BEGIN a->a->zero(); a->a->objective = 0; GUARD_END_INT }
 double tclb_adjoint_objective(tclb_adjoint_h *a) { return a->a->objective; }
 int tclb_adjoint_want_setting(tclb_adjoint_h *a, tclb_domain_h *h, const char *names_csv) {

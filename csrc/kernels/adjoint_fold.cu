@@ -83,3 +83,54 @@ extern "C" int tclb_adjoint_add_into(void *dst, const void *src, long long n, in
     else k_add_into<float><<<(unsigned)nb, tb, 0, (cudaStream_t)stream>>>((float *)dst, (const float *)src, n);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
+
+// Ghost fold between two subdomains: the ghost cells of `src` on its (dy,dz) side are images of interior cells of the
+// neighbour `dst` on that side; their adjoint values are added there and cleared.  (dy,dz) = (0,0) is not a ghost side.
+namespace {
+template <class T>
+__host__ __device__ inline void fold_pair_cell(T *dst, int dny, int dnz, T *src, int sny, int snz, int nx, int gy, int gz, int dy, int dz,
+                                               int f, int iy, int iz, int x) {
+    // (iy, iz) enumerate the ghost region of src: iy in [0, dy ? gy : sny), iz in [0, dz ? gz : snz)
+    const int sy = dy > 0 ? sny + iy : (dy < 0 ? -gy + iy : iy), sz = dz > 0 ? snz + iz : (dz < 0 ? -gz + iz : iz);
+    const int ty = dy > 0 ? iy : (dy < 0 ? dny - gy + iy : iy), tz = dz > 0 ? iz : (dz < 0 ? dnz - gz + iz : iz);
+    const int sNY = sny + 2 * gy, sNZ = snz + 2 * gz, dNY = dny + 2 * gy, dNZ = dnz + 2 * gz;
+    T *ps = src + (size_t)f * ((size_t)nx * sNY * sNZ) + ((size_t)(sz + gz) * sNY + (sy + gy)) * nx + x;
+    const T v = *ps;
+    if (v == (T)0) return;
+    T *pd = dst + (size_t)f * ((size_t)nx * dNY * dNZ) + ((size_t)(tz + gz) * dNY + (ty + gy)) * nx + x;
+#ifdef __CUDA_ARCH__
+    atomicAdd(pd, v);
+#else
+    *pd += v;
+#endif
+    *ps = (T)0;
+}
+template <class T>
+__global__ void k_fold_pair(T *dst, int dny, int dnz, T *src, int sny, int snz, int nx, int gy, int gz, int dy, int dz, int ry) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= nx) return;
+    const int iy = blockIdx.y % ry, iz = blockIdx.y / ry;
+    fold_pair_cell(dst, dny, dnz, src, sny, snz, nx, gy, gz, dy, dz, (int)blockIdx.z, iy, iz, x);
+}
+}  // namespace
+extern "C" int tclb_adjoint_fold_pair(void *dst, int dny, int dnz, void *src, int sny, int snz, int real_size, int on_device, int nfields,
+                                      int nx, int gy, int gz, int dy, int dz, void *stream) {
+    const int ry = dy ? gy : sny, rz = dz ? gz : snz;
+    if (ry <= 0 || rz <= 0 || (dy == 0 && dz == 0)) return 0;
+    if (!on_device) {
+        for (int f = 0; f < nfields; f++)
+            for (int iz = 0; iz < rz; iz++)
+                for (int iy = 0; iy < ry; iy++)
+                    for (int x = 0; x < nx; x++) {
+                        if (real_size == 8) fold_pair_cell((double *)dst, dny, dnz, (double *)src, sny, snz, nx, gy, gz, dy, dz, f, iy, iz, x);
+                        else fold_pair_cell((float *)dst, dny, dnz, (float *)src, sny, snz, nx, gy, gz, dy, dz, f, iy, iz, x);
+                    }
+        return 0;
+    }
+    const int tb = nx >= 128 ? 128 : 32;
+    if ((long long)ry * rz > 65535 || nfields > 65535) return -1;
+    dim3 grid((nx + tb - 1) / tb, ry * rz, nfields);
+    if (real_size == 8) k_fold_pair<double><<<grid, tb, 0, (cudaStream_t)stream>>>((double *)dst, dny, dnz, (double *)src, sny, snz, nx, gy, gz, dy, dz, ry);
+    else k_fold_pair<float><<<grid, tb, 0, (cudaStream_t)stream>>>((float *)dst, dny, dnz, (float *)src, sny, snz, nx, gy, gz, dy, dz, ry);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}

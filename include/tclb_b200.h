@@ -119,6 +119,9 @@ int tclb_adjoint_record(tclb_adjoint_h *, int n);
 int tclb_adjoint_reverse(tclb_adjoint_h *);
 int tclb_adjoint_steady(tclb_adjoint_h *, int n);
 int tclb_adjoint_zero(tclb_adjoint_h *);
+/* bound the number of stored states of the tape (0 = every iteration): checkpoints + recomputation in reverse() */
+int tclb_adjoint_set_tape_frames(tclb_adjoint_h *, int n);
+int tclb_adjoint_tape_frames(tclb_adjoint_h *);       /* states currently held */
 double tclb_adjoint_objective(tclb_adjoint_h *);
 /* gradients with respect to non-zonal settings (comma separated names; call before record()); the value returned is
  * the total derivative, following the derived-settings chain (e.g. nu -> omega) */

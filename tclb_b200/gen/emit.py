@@ -509,6 +509,23 @@ template <int GMODE> TCLB_HD int k_zone_index(const KArgs &a) {
             A(f"    case {i}: return (real_t){float(f.shift)!r};")
     A("    default: return (real_t)0;\n    }\n}")
 
+    # adjoint build: ids of the (field, offset) pairs a stage can read through stencil accessors
+    st_fields = [(i, f) for i, f in enumerate(m.fields) if not f.simple_access]
+    A("#ifdef TCLB_AD")
+    A("TCLB_HD int ad_stencil_id(int fi, int dx, int dy, int dz) {\n    switch (fi) {")
+    off = 0
+    st_table = []
+    for i, f in st_fields:
+        ex, ey, ez = f.maxx - f.minx + 1, f.maxy - f.miny + 1, f.maxz - f.minz + 1
+        A(f"    case {i}: return {off} + ((dz - ({f.minz})) * {ey} + (dy - ({f.miny}))) * {ex} + (dx - ({f.minx}));")
+        for dz_ in range(f.minz, f.maxz + 1):
+            for dy_ in range(f.miny, f.maxy + 1):
+                for dx_ in range(f.minx, f.maxx + 1):
+                    st_table.append((i, dx_, dy_, dz_))
+        off += ex * ey * ez
+    A("    default: return -(1 << 29);\n    }\n}")
+    A(f"constexpr int AD_N_STENCIL = {len(st_table)};")
+    A("#endif")
     autosym = int(getattr(m, "autosym", 0) or 0)
     A(f"#define TCLB_AUTOSYM {autosym}")
     if autosym:
@@ -552,6 +569,9 @@ struct Node {
     flag_t n_type;
     real_t *gacc_;        // per-node Globals accumulators: a strip of shared memory on the GPU (no registers held
                           // across the collision), a local array on the host; element i lives at gacc_[i * GSTRIDE]
+#ifdef TCLB_AD
+    int ad_lo_ = -(1 << 30);   // first stencil-read input id seeded in this pass (adjoint build), see load_field_plain
+#endif
 """)
     for d in members:
         A("    " + d)
@@ -607,7 +627,14 @@ struct Node {
     TCLB_HD real_t load_field_plain(int fi, int dx, int dy, int dz) const {
         int xx = tclbrt::wrapx(n_x, dx, ka_.nx);
         long long i = ((long long)(n_z + dz + GZ) * ka_.NY + (n_y + dy + GY)) * ka_.nx + xx;
-        return TCLB_LD(ka_.in[fi * ka_.fstride + i], field_shift(fi));
+        real_t v = TCLB_LD(ka_.in[fi * ka_.fstride + i], field_shift(fi));
+#ifdef TCLB_AD
+        // adjoint build: a read through a stencil accessor is an input of the stage like a pulled density; the directions
+        // of the current chunk that stand for (field, offset) pairs are ad_lo_ .. ad_lo_ + TCLB_AD_DIRS - 1
+        const int j = ad_stencil_id(fi, dx, dy, dz) - ad_lo_;
+        if (j >= 0 && j < TCLB_AD_DIRS) v.d[j] = 1;
+#endif
+        return v;
     }
 #if TCLB_AUTOSYM > 0
     // option autosym (reference SymmetryAccess, src/LatticeAccess.inc.cpp.Rt:376-447): a read that crosses a mirror plane
@@ -777,10 +804,19 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
         # list; warp 0 also announces the byte count.  `row0` = index of the tile's first node in a field
         A(f"TCLB_D void ring_issue_rows_{si}(const KArgs &a, unsigned char *sb, void *bar, long long row0, int wid) {{")
         if ok:
-            A(f"    if (wid == 0) tclbrt::mbar_arrive_expect_tx(bar, (unsigned)(RING_ROWS_{si} * TCLB_TILE_X * (int)sizeof(storage_t) + TCLB_TILE_X * (int)sizeof(flag_t)));")
-            for k, (di, d) in enumerate(ld):
-                A(f"    if (wid == {k % 4}) tclbrt::bulk_g2s(sb + {k} * RING_ROW + 16, a.ldp[{di}] + row0, TCLB_TILE_X * (unsigned)sizeof(storage_t), bar);")
-            A(f"    if (wid == {len(ld) % 4}) tclbrt::bulk_g2s(sb + RING_ROWS_{si} * RING_ROW, a.flags + row0, TCLB_TILE_X * (unsigned)sizeof(flag_t), bar);")
+            # one switch on the warp number (not one test per row: the tests were 6 % of the kernel's instructions)
+            rows = [(k, f"a.ldp[{di}] + row0", "TCLB_TILE_X * (unsigned)sizeof(storage_t)", f"{k} * RING_ROW + 16") for k, (di, d) in enumerate(ld)]
+            rows.append((len(ld), "a.flags + row0", "TCLB_TILE_X * (unsigned)sizeof(flag_t)", f"RING_ROWS_{si} * RING_ROW"))
+            A("    switch (wid) {")
+            for w in range(4):
+                A(f"    case {w}:")
+                if w == 0:
+                    A(f"        tclbrt::mbar_arrive_expect_tx(bar, (unsigned)(RING_ROWS_{si} * TCLB_TILE_X * (int)sizeof(storage_t) + TCLB_TILE_X * (int)sizeof(flag_t)));")
+                for k, src, nbytes, dst in rows:
+                    if k % 4 == w:
+                        A(f"        tclbrt::bulk_g2s(sb + {dst}, {src}, {nbytes}, bar);")
+                A("        break;")
+            A("    }")
         A("}")
         if ok and edges:
             # one packed word per edge element in constant memory: row | field << 8 | (position + 8) << 16 | (dy + 2) << 24 |
@@ -847,8 +883,22 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     loaded = [[(di, d) for di, d in enumerate(m.densities) if d.load.get(s.name)] for s in m.stages]
     A("TCLB_HD int ad_inputs_of_stage(int s) {\n    switch (s) {")
     for si in range(len(m.stages)):
+        A(f"    case {si}: return {len(loaded[si])} + AD_N_STENCIL;")
+    A("    default: return 0;\n    }\n}")
+    A("TCLB_HD int ad_loaded_of_stage(int s) {\n    switch (s) {")
+    for si in range(len(m.stages)):
         A(f"    case {si}: return {len(loaded[si])};")
     A("    default: return 0;\n    }\n}")
+    # scatter of the stencil inputs: id -> (field, offset)
+    A("TCLB_HD void ad_scatter_stencil(const KArgs &a, base_t *adj_in, int x, int y, int z, int id, base_t g) {")
+    A("    if (g == (base_t)0) return;")
+    A("    int fi = 0, dx = 0, dy = 0, dz = 0;\n    switch (id) {")
+    for k, (i, dx_, dy_, dz_) in enumerate(st_table):
+        A(f"    case {k}: fi = {i}; dx = {dx_}; dy = {dy_}; dz = {dz_}; break;")
+    A("    default: return;\n    }")
+    A("    const int xx = tclbrt::wrapx(x, dx, a.nx);")
+    A("    ad_add(adj_in + (long long)fi * a.fstride + ((long long)(z + dz + GZ) * a.NY + (y + dy + GY)) * a.nx + xx, g);")
+    A("}")
     for si, s in enumerate(m.stages):
         A(f"template <int GMODE> TCLB_HD void ad_seed_stage_{si}(Node<GMODE> &n, int c) {{")
         for k, (di, d) in enumerate(loaded[si]):

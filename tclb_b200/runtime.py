@@ -169,6 +169,8 @@ def core():
         "tclb_adjoint_reverse": [C.c_void_p],
         "tclb_adjoint_steady": [C.c_void_p, C.c_int],
         "tclb_adjoint_zero": [C.c_void_p],
+        "tclb_adjoint_set_tape_frames": [C.c_void_p, C.c_int],
+        "tclb_adjoint_tape_frames": [C.c_void_p],
         "tclb_adjoint_objective": [C.c_void_p],
         "tclb_adjoint_get_field": [C.c_void_p, C.c_void_p, C.c_char_p, C.c_void_p],
         "tclb_adjoint_want_setting": [C.c_void_p, C.c_void_p, C.c_char_p],
@@ -476,6 +478,13 @@ class Adjoint:
 
     def zero(self):
         _check(self.lib.tclb_adjoint_zero(self.h))
+
+    def set_tape_frames(self, n: int):
+        """keep at most n stored states: checkpoints at a doubling stride during record(), recomputation in reverse()"""
+        _check(self.lib.tclb_adjoint_set_tape_frames(self.h, int(n)))
+
+    def tape_frames(self) -> int:
+        return int(self.lib.tclb_adjoint_tape_frames(self.h))
 
     @property
     def objective(self) -> float:

@@ -1,0 +1,178 @@
+"""Adjoint beyond one stage on one subdomain (reference: multi-stage Action_*_Adj of src/Lattice.cu.Rt:542-613, the
+adjoint scatter of stencil reads src/LatticeAccess.inc.cpp.Rt:349-373, snapshot levels :46-61,843-890):
+  * reads through stencil accessors are differentiated (d2q9_kuper lowered from the reference's files: phi(dx,dy));
+  * actions of several stages are swept back stage by stage (d2q9_poison_boltzmann: 3 stages);
+  * several subdomains give the gradient of one (ghost fold into the neighbour's buffer);
+  * a bounded tape (checkpoints + recomputation) gives the gradient of the full tape.
+Every gradient is checked against central differences of the recorded objective along a random direction."""
+import os
+
+import numpy as np
+import pytest
+
+from tclb_b200 import build
+from tclb_b200.runtime import Adjoint, Domain, Model
+
+
+def _objective_sum(d, n):
+    tot = 0.0
+    for _ in range(n):
+        d.iterate(1, globals_every=True)
+        tot += d.globals()["Objective"]
+    return tot
+
+
+def _directional_check(d, m, n, fields, tol, frames=0, seed=3):
+    base = {f: d.get_field(f).astype(np.float64) for f in m.fields}
+    adj = Adjoint(d)
+    if frames:
+        adj.set_tape_frames(frames)
+    adj.record(n)
+    J0 = adj.objective
+    held = adj.tape_frames()
+    adj.reverse()
+    grad = {f: adj.get_field(f).astype(np.float64) for f in fields}
+    adj.close()
+    rng = np.random.default_rng(seed)
+    direction = {f: rng.standard_normal(base[f].shape) for f in fields}
+    predicted = sum(float((grad[f] * direction[f]).sum()) for f in fields)
+    eps = 1e-6
+
+    def J(sign):
+        for f in m.fields:
+            d.set_field(f, base[f] + (sign * eps * direction[f] if f in direction else 0.0))
+        return _objective_sum(d, n)
+
+    fd = (J(+1) - J(-1)) / (2 * eps)
+    assert J0 != 0.0 and predicted != 0.0
+    assert abs(fd - predicted) <= tol * max(abs(fd), abs(predicted)), (fd, predicted)
+    return grad, held
+
+
+def _terminal_check(d, m, n, tol, seed=5):
+    """cost J = <w, state after n iterations>: w is seeded into the adjoint buffers before the backward sweep"""
+    rng = np.random.default_rng(seed)
+    base = {f: d.get_field(f).astype(np.float64) for f in m.fields}
+    w = {f: rng.standard_normal(base[f].shape) for f in m.fields}
+    direction = {f: rng.standard_normal(base[f].shape) for f in m.fields}
+    adj = Adjoint(d)
+    adj.record(n)
+    for f in m.fields:
+        adj.set_field(f, w[f])
+    adj.reverse()
+    predicted = sum(float((adj.get_field(f) * direction[f]).sum()) for f in m.fields)
+    adj.close()
+    eps = 1e-6
+
+    def J(sign):
+        for f in m.fields:
+            d.set_field(f, base[f] + sign * eps * direction[f])
+        d.iterate(n)
+        return sum(float((w[f] * d.get_field(f)).sum()) for f in m.fields)
+
+    fd = (J(+1) - J(-1)) / (2 * eps)
+    assert predicted != 0.0 and abs(fd - predicted) <= tol * max(abs(fd), abs(predicted)), (fd, predicted)
+
+
+def _channel(m, shape, backend="cpu", nranks=1):
+    nx, ny, nz = shape
+    d = Domain(m, shape, backend, nranks=nranks)
+    fl = np.full((nz, ny, nx), m.flag("MRT"), dtype=np.uint32)
+    fl[:, 0, :] = m.flag("Wall")
+    fl[:, -1, :] = m.flag("Wall")
+    fl[:, ny // 3:ny // 3 + 3, nx // 4:nx // 4 + 3] = m.flag("Wall")
+    d.set_flags(fl)
+    return d
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 4])
+def test_adjoint_on_several_subdomains(built, nranks):
+    build.build_model_lib("d2q9", "double")
+    build.build_adjoint_lib("d2q9", "double")
+    m = Model("d2q9", "double")
+    d = _channel(m, (24, 16, 1), nranks=nranks)
+    d.set_setting("Viscosity", 0.05); d.set_setting("GravitationX", 1e-4)
+    d.set_setting("OutletFluxInObj", 1.0); d.set_setting("PressureLossInObj", 0.3)
+    fl = d.get_flags()
+    fl[:, 1:-1, 3] |= m.flag("Inlet"); fl[:, 1:-1, -4] |= m.flag("Outlet")
+    d.set_flags(fl)
+    d.init(); d.iterate(10)
+    grad, _ = _directional_check(d, m, 6, list(m.fields), 1e-6)
+    d.close()
+    if nranks > 1:
+        ref = test_adjoint_on_several_subdomains.ref
+        for f in grad:
+            assert np.abs(grad[f] - ref[f]).max() <= 1e-13 * max(1.0, np.abs(ref[f]).max()), f
+    else:
+        test_adjoint_on_several_subdomains.ref = grad
+
+
+def test_bounded_tape_recomputes_to_the_same_gradient(built):
+    build.build_model_lib("d2q9", "double")
+    build.build_adjoint_lib("d2q9", "double")
+    m = Model("d2q9", "double")
+    grads = []
+    for frames in (0, 6):
+        d = _channel(m, (24, 16, 1))
+        d.set_setting("Viscosity", 0.05); d.set_setting("GravitationX", 1e-4)
+        d.set_setting("OutletFluxInObj", 1.0)
+        fl = d.get_flags(); fl[:, 1:-1, -4] |= m.flag("Outlet"); d.set_flags(fl)
+        d.init(); d.iterate(5)
+        adj = Adjoint(d)
+        if frames:
+            adj.set_tape_frames(frames)
+        adj.record(53)
+        held = adj.tape_frames()
+        state_after = {f: d.get_field(f) for f in m.fields}
+        adj.reverse()
+        grads.append({f: adj.get_field(f) for f in m.fields})
+        assert all(np.array_equal(d.get_field(f), state_after[f]) for f in m.fields)      # the lattice is put back where it was
+        assert held == 53 if not frames else held <= 4
+        adj.close(); d.close()
+    for f in grads[0]:
+        assert np.array_equal(grads[0][f], grads[1][f]), f          # recomputation repeats the same arithmetic
+
+
+def test_multi_stage_action_adjoint(built):
+    """3-stage Iteration (BaseIteration, CalcPsi, CalcSubiter): the model has no Globals, so the cost is a terminal one,
+    J = <w, state after n iterations>, seeded into the adjoint before the sweep"""
+    build.build_model_lib("d2q9_poison_boltzmann", "double")
+    build.build_adjoint_lib("d2q9_poison_boltzmann", "double")
+    m = Model("d2q9_poison_boltzmann", "double")
+    assert len(m.actions["Iteration"]) == 3
+    nx, ny, n = 16, 12, 4
+    d = Domain(m, (nx, ny, 1), "cpu", nranks=1)
+    first = [k for k, v in m.nodetypes.items() if v[0] != 0][0]
+    fl = np.full((1, ny, nx), m.flag("BGK") if "BGK" in m.nodetypes else m.flag(first), dtype=np.uint32)
+    d.set_flags(fl)
+    d.init()
+    rng = np.random.default_rng(5)
+    for f in m.fields:
+        a = d.get_field(f)
+        d.set_field(f, a + 1e-2 * rng.standard_normal(a.shape))
+    d.iterate(3)
+    _terminal_check(d, m, n, 1e-6)
+    d.close()
+
+
+def test_stencil_reads_are_differentiated(built, reference_dir):
+    build.build_from_dir(os.path.join(reference_dir, "models/multiphase/d2q9_kuper"), precision="double")
+    build.build_adjoint_lib("ref_d2q9_kuper", "double")
+    m = Model("ref_d2q9_kuper", "double")
+    nx, ny = 20, 14
+    d = Domain(m, (nx, ny, 1), "cpu", nranks=1)
+    fl = np.full((1, ny, nx), m.flag("MRT") if "MRT" in m.nodetypes else m.flag("BGK"), dtype=np.uint32)
+    fl[:, 0, :] = m.flag("Wall"); fl[:, -1, :] = m.flag("Wall")
+    d.set_flags(fl)
+    for k, v in (("omega", 1.0), ("nu", 0.1666), ("Density", 1.0), ("Temperature", 0.56), ("FAcc", 1.0), ("Magic", 0.01), ("MagicA", -0.152),
+                 ("MagicF", -0.6666666), ("GravitationX", 1e-5), ("Wetting", 1.0)):
+        if k in m.settings or k in m.zonesettings:
+            d.set_setting(k, v)
+    d.init()
+    rng = np.random.default_rng(9)
+    for f in m.fields:
+        a = d.get_field(f)
+        d.set_field(f, a * (1.0 + 1e-3 * rng.standard_normal(a.shape)))
+    d.iterate(2)
+    _terminal_check(d, m, 4, 1e-5)
+    d.close()
