@@ -138,6 +138,8 @@ class AcAdjoint : public GenericAction {
         std::string type = node->attr("type");
         if (type.empty()) type = node->has_attr("Iterations") ? "steady" : "unsteady";
         Adjoint *A = solver->need_adjoint();
+        // tape="n": keep at most n states; the sweep recomputes the iterations in between (the reference's snapshot levels)
+        if (node->has_attr("tape")) A->set_tape_frames(std::max(2, atoi(node->attr("tape").c_str())));
         if (type == "unsteady" && solver->recording) {
             // inside an evaluation of <Optimize>/<FDTest> (reference case files put the adjoint run there): the tape is
             // already being recorded and the optimiser sweeps it back itself

@@ -113,6 +113,18 @@ TCLB_D void mbar_wait(void *bar, unsigned parity) {
         "TCLB_MBAR_DONE:\n"
         "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+// true in exactly one lane of a fully converged warp (elect.sync): unlike `lane == 0` the compiler then knows a single thread
+// issues what follows, so a bulk copy is one instruction instead of a loop over the active lanes
+TCLB_D bool elect_one() {
+    unsigned pred = 0;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(pred));
+    return pred != 0;
+}
 // global -> shared bulk copy (size and both addresses multiples of 16 bytes); completion is counted on `bar`
 TCLB_D void bulk_g2s(void *dst, const void *src, unsigned bytes, void *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"

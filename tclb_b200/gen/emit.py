@@ -373,6 +373,16 @@ typedef base_t storage_t;
     # bulk-copy ring), separately for launches without / with Globals, and the occupancy the persistent kernels are built for
     A("#ifndef TCLB_KERNEL_DEFAULT\n#define TCLB_KERNEL_DEFAULT %d\n#endif" % int(tun.get("kernel", 0)))
     A("#ifndef TCLB_KERNEL_DEFAULT_G\n#define TCLB_KERNEL_DEFAULT_G %d\n#endif" % int(tun.get("kernel_g", 2)))
+    # interior fast path of the GPU stage kernels: a warp whose nodes carry no bits outside the collision and zone groups runs
+    # a copy of the stage in which those bits are known to be zero (the boundary dispatch and its register shuffles fold away)
+    plain_mask = 0
+    for g in m.nodetypegroups:
+        if g.name not in ("COLLISION", "SETTINGZONE"):
+            plain_mask |= int(g.mask)
+    A("#ifndef TCLB_RING_SLOTS\n#define TCLB_RING_SLOTS %d\n#endif" % int(tun.get("ring_slots", 1)))
+    A("#ifndef TCLB_ELECT\n#define TCLB_ELECT %d\n#endif" % int(tun.get("elect", 0)))
+    A("#define TCLB_PLAIN_MASK %du" % plain_mask)
+    A("#ifndef TCLB_FASTPATH\n#define TCLB_FASTPATH %d\n#endif" % int(tun.get("fastpath", 0)))
     A("#ifndef TCLB_PERSIST_MIN_BLOCKS\n#ifdef TCLB_DOUBLE\n#define TCLB_PERSIST_MIN_BLOCKS %d\n#else\n#define TCLB_PERSIST_MIN_BLOCKS %d\n#endif\n#endif"
       % (int(tun.get("persist_min_blocks_double", 3)), int(tun.get("persist_min_blocks_float", 5))))
     A("namespace {")
@@ -847,7 +857,7 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     for si in range(len(m.stages)):
         A(f"    if (S == {si}) ring_issue_edges_{si}(a, sb, lane, row0, x0);")
     A("}")
-    A("template <int S> constexpr bool ring_ok() { return " + " || ".join(f"(S == {si} && RING_OK_{si})" for si in range(len(m.stages))) + "; }")
+    A("template <int S> constexpr bool ring_ok() { return " + " || ".join(f"(S == {si} && RING_OK_{si} && RING_BYTES_{si} * TCLB_RING_SLOTS <= 100 * 1024)" for si in range(len(m.stages))) + "; }")
     A("template <int S> constexpr int ring_bytes() { return " + " + ".join(f"(S == {si} ? RING_BYTES_{si} : 0)" for si in range(len(m.stages))) + "; }")
     A("#endif")
     A("template <int GMODE> TCLB_HD void load_all(Node<GMODE> &n, const KArgs &a, int x, int i0, int im, int ip) {")

@@ -203,6 +203,8 @@ CudaDeviceFunction real_t getKinE() {
 	}
 }""")
     A("CudaDeviceFunction void RunBoundaries() {")
+    # most nodes carry no boundary bits: leave before the dispatch, so the arms' register shuffles stay off the common path
+    A("\tif ((NodeType & (NODE_ADDITIONALS | NODE_BOUNDARY" + (" | NODE_HO_BOUNDARY" if opt["IB"] else "") + ")) == 0) return;")
     if opt["IB"]:
         A("\tif ((NodeType & NODE_HO_BOUNDARY) == NODE_IB) InterpolatedBounceBack();")
     A("""	switch (NodeType & NODE_ADDITIONALS) {

@@ -239,6 +239,24 @@ class Model:
     def bytes_per_update(self) -> int:
         return 2 * len(self.fields) * self.d.storage_size + self.d.flag_size
 
+    def action_traffic(self, action: str = "Iteration") -> Dict[str, object]:
+        """Compulsory memory traffic of one run of an action, from the stage tables the generator emitted (not an estimate):
+        per stage, every field it loads as a density or reads through a stencil accessor counts once (its shifted copies
+        come from the same rows), every field it saves counts once, plus the flag.  The reference's own accounting
+        (src/main.cpp:127) assumes one stage that reads and writes every field: 2*nFields*sizeof + flag."""
+        d = self.d
+        dens_field = [int(d.densities[i].field_index) for i in range(d.n_densities)]
+        per_stage, total = [], 0
+        for s in self.actions[action]:
+            st = d.stages[s]
+            rd = set(dens_field[i] for i in range(d.n_densities) if st.load_density[i])
+            rd |= set(f for f in range(d.n_fields) if st.read_field[f])
+            wr = set(f for f in range(d.n_fields) if st.save_field[f])
+            b = (len(rd) + len(wr)) * int(d.storage_size) + int(d.flag_size)
+            per_stage.append({"stage": _s(st.name), "fields_read": len(rd), "fields_written": len(wr), "bytes": b})
+            total += b
+        return {"action": action, "bytes_per_update": total, "stages": per_stage}
+
     def flag(self, *names: str) -> int:
         v = 0
         for n in names:

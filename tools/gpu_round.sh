@@ -10,5 +10,5 @@ python bench.py --config pf_velocity --steps 20 --warmup 5 2>> gpurun_out/bench.
 for m in ref_d3q27_cumulant ref_d3q19; do echo "== $m no globals"; python bench.py --model $m --shape 512,512,512 --no-globals --steps 20 --warmup 5 2>> gpurun_out/bench.err | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['roofline']['fraction_of_measured_hbm'])"; done | tee gpurun_out/ref_lowered.txt
 python tools/ncu_window.py > gpurun_out/window_plain.log 2>&1 && \
 ncu --set full --clock-control none --import-source on --profile-from-start off -f -o gpurun_out/prof_window python tools/ncu_window.py > gpurun_out/ncu_window.log 2>&1
-tail -3 gpurun_out/window_plain.log gpurun_out/ncu_window.log
+tail -n 3 gpurun_out/window_plain.log; tail -n 3 gpurun_out/ncu_window.log
 ls -la gpurun_out/*.ncu-rep

@@ -8,7 +8,7 @@
 Window contents (512x256x256 fp32 unless noted; every launch is warmed up before the window opens):
   d3q27_cumulant   ring kernel with Globals (k_stage_persist<0,1,1> + k_fold_globals<1> + k_publish_globals),
                    classic kernel with Globals (k_stage<0,1>), classic without Globals (k_stage<0,0>),
-                   k_quantity (U, Rho), k_color
+                   k_quantity (U, P), k_color
   ref_d3q27_cumulant, ref_d3q19   classic kernel without Globals (the lowered reference models)
 """
 import ctypes
@@ -58,7 +58,7 @@ def main():
     os.environ["TCLB_KERNEL"] = "ring"
     m, d = channel("d3q27_cumulant", SHAPE)
     d.iterate(3, globals_every=True)
-    d.get_quantity("U"); d.get_quantity("Rho"); d.color(SHAPE[2] // 2)
+    d.get_quantity("U"); d.get_quantity("P"); d.color(SHAPE[2] // 2)
     d.sync()
 
     def native():
@@ -67,7 +67,7 @@ def main():
         os.environ["TCLB_KERNEL"] = "classic"
         d.iterate(1, globals_every=True)
         d.iterate(1)
-        d.get_quantity("U"); d.get_quantity("Rho"); d.color(SHAPE[2] // 2)
+        d.get_quantity("U"); d.get_quantity("P"); d.color(SHAPE[2] // 2)
         d.sync()
 
     os.environ["TCLB_KERNEL"] = "classic"
