@@ -2,6 +2,7 @@
 // the table in SURVEY.md section 2.3 lists them).  Behaviour is re-stated per class below with the
 // reference file it mirrors.
 #include "handler.h"
+#include "../host/rfi_bridge.h"
 #include "../core/common.h"
 #include "../host/sampler.h"
 #include <algorithm>
@@ -860,29 +861,47 @@ TCLB_REGISTER_HANDLER("SaveBinary", CbSaveBinary)
 class CbSaveMemoryDump : public CbSaveBinary {};
 TCLB_REGISTER_HANDLER("SaveMemoryDump", CbSaveMemoryDump)
 
-// <RemoteForceInterface integrator="SIMPLEPART" [omega torque]>: particle coupling.  The reference connects to an external
-// program over MPI inter-communicators (acRemoteForceInterface.cpp:7-110); here the integrator runs in this process
-// (csrc/host/particles.h).  Its configuration is the <SimplePart> child element, or the file given with --simplepart.
+// <RemoteForceInterface integrator="NAME" [omega torque] [spawn="program args" | connect="/path/to/socket"]>: particle coupling.
+// The reference connects to an external program over MPI inter-communicators (acRemoteForceInterface.cpp:7-110, MPMD.hpp).
+// Here: integrator="SIMPLEPART" without spawn/connect runs the integrator in this process (csrc/host/particles.h; its
+// configuration is the <SimplePart> child element, or the file given with --simplepart); with spawn= or connect= the
+// integrator is ANOTHER PROGRAM reached over a local socket with the same sizes/particles/forces sequence
+// (csrc/host/rfi_bridge.h; bin/tclb-integrator provides `simplepart` and `empty`).
 class AcRemoteForceInterface : public Action {
   public:
     int init() override {
         Action::init();
         std::string name = node->attr("integrator");
         if (name.empty()) { logf(L_ERROR, "You must specify RemoteForceInterface integrator name"); return -1; }
-        if (name != "SIMPLEPART" && name != "simplepart") {
-            logf(L_ERROR, "RemoteForceInterface: integrator %s is not available (built in: SIMPLEPART)", name.c_str());
-            return -1;
+        if (node->has_attr("spawn") || node->has_attr("connect")) {
+            std::unique_ptr<RemoteIntegrator> ri(new RemoteIntegrator());
+            const int workers = (int)solver->domain->local.size();
+            bool ok;
+            if (node->has_attr("spawn")) {
+                logf(L_OUTPUT, "Connecting RFI to %s (starting: %s)", name.c_str(), node->attr("spawn").c_str());
+                ok = ri->spawn(node->attr("spawn"), workers, node->attr_bool("omega"), node->attr_bool("torque"));
+            } else {
+                logf(L_OUTPUT, "Connecting RFI to %s (socket %s)", name.c_str(), node->attr("connect").c_str());
+                ok = ri->connect_to(node->attr("connect"), workers, node->attr_bool("omega"), node->attr_bool("torque"));
+            }
+            if (!ok) { logf(L_ERROR, "RemoteForceInterface: %s", ri->error.c_str()); return -1; }
+            solver->integrator.reset(ri.release());
+        } else {
+            if (name != "SIMPLEPART" && name != "simplepart") {
+                logf(L_ERROR, "RemoteForceInterface: integrator %s is not built in (built in: SIMPLEPART); give spawn=\"program ...\" or connect=\"socket\" for an external one", name.c_str());
+                return -1;
+            }
+            std::unique_ptr<XmlDocument> doc;
+            const XmlNode *cfg = node->child("SimplePart");
+            if (!solver->opt.simplepart_config.empty()) {
+                doc.reset(new XmlDocument());
+                doc->load_file(solver->opt.simplepart_config);
+                cfg = doc->child("SimplePart");
+            }
+            if (!cfg) { logf(L_ERROR, "RemoteForceInterface: no <SimplePart> configuration (child element or --simplepart file)"); return -1; }
+            logf(L_OUTPUT, "Connecting RFI to %s (in-process)", name.c_str());
+            solver->integrator.reset(new SimplePart(cfg, solver->outpath + "_SP_Log.csv", node->attr_bool("omega"), node->attr_bool("torque")));
         }
-        std::unique_ptr<XmlDocument> doc;
-        const XmlNode *cfg = node->child("SimplePart");
-        if (!solver->opt.simplepart_config.empty()) {
-            doc.reset(new XmlDocument());
-            doc->load_file(solver->opt.simplepart_config);
-            cfg = doc->child("SimplePart");
-        }
-        if (!cfg) { logf(L_ERROR, "RemoteForceInterface: no <SimplePart> configuration (child element or --simplepart file)"); return -1; }
-        logf(L_OUTPUT, "Connecting RFI to %s (in-process)", name.c_str());
-        solver->integrator.reset(new SimplePart(cfg, solver->outpath + "_SP_Log.csv", node->attr_bool("omega"), node->attr_bool("torque")));
         Solver *s = solver;
         auto box_of = [s](int r) {
             const Box &b = s->domain->dec.boxes[r];

@@ -112,6 +112,10 @@ def build_core(force: bool = False, verbose: bool = False) -> Path:
         BINDIR.mkdir(exist_ok=True)
         _run(["g++"] + CXX_FLAGS + incs + [str(main_src), "-o", str(BINDIR / "tclb"), "-L", str(LIBDIR), "-ltclb_core",
                                           "-Wl,-rpath,$ORIGIN/../tclb_b200/_lib", "-ldl"])
+    integ_src = ROOT / "csrc" / "integrator_main.cpp"
+    if integ_src.exists():
+        _run(["g++"] + CXX_FLAGS + incs + [str(integ_src), "-o", str(BINDIR / "tclb-integrator"), "-L", str(LIBDIR), "-ltclb_core",
+                                          "-Wl,-rpath,$ORIGIN/../tclb_b200/_lib", "-ldl"])
     cmp_src = ROOT / "csrc" / "compare.cpp"
     if cmp_src.exists():
         _run(["g++"] + CXX_FLAGS + incs + [str(cmp_src), "-o", str(BINDIR / "compare"), "-L", str(LIBDIR), "-ltclb_core",

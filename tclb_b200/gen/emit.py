@@ -381,6 +381,8 @@ typedef base_t storage_t;
             plain_mask |= int(g.mask)
     A("#ifndef TCLB_RING_SLOTS\n#define TCLB_RING_SLOTS %d\n#endif" % int(tun.get("ring_slots", 1)))
     A("#ifndef TCLB_ELECT\n#define TCLB_ELECT %d\n#endif" % int(tun.get("elect", 0)))
+    A("// true inside the node code of the persistent kernels (compile-time constant of the Node<GMODE> instance)")
+    A("#define TCLB_NODE_PERSISTENT ((GMODE & 8) != 0)")
     A("#define TCLB_PLAIN_MASK %du" % plain_mask)
     A("#ifndef TCLB_FASTPATH\n#define TCLB_FASTPATH %d\n#endif" % int(tun.get("fastpath", 0)))
     A("#ifndef TCLB_PERSIST_MIN_BLOCKS\n#ifdef TCLB_DOUBLE\n#define TCLB_PERSIST_MIN_BLOCKS %d\n#else\n#define TCLB_PERSIST_MIN_BLOCKS %d\n#endif\n#endif"

@@ -203,8 +203,9 @@ CudaDeviceFunction real_t getKinE() {
 	}
 }""")
     A("CudaDeviceFunction void RunBoundaries() {")
-    # most nodes carry no boundary bits: leave before the dispatch, so the arms' register shuffles stay off the common path
-    A("\tif ((NodeType & (NODE_ADDITIONALS | NODE_BOUNDARY" + (" | NODE_HO_BOUNDARY" if opt["IB"] else "") + ")) == 0) return;")
+    # Persistent kernel only (measured: ring +6 %, one-block-per-tile kernel -22 % with the same line): most nodes carry no
+    # boundary bits, leaving before the dispatch keeps the arms' register shuffles off the common path
+    A("\tif (TCLB_NODE_PERSISTENT && (NodeType & (NODE_ADDITIONALS | NODE_BOUNDARY" + (" | NODE_HO_BOUNDARY" if opt["IB"] else "") + ")) == 0) return;")
     if opt["IB"]:
         A("\tif ((NodeType & NODE_HO_BOUNDARY) == NODE_IB) InterpolatedBounceBack();")
     A("""	switch (NodeType & NODE_ADDITIONALS) {
