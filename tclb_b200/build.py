@@ -165,6 +165,19 @@ def precision_flags(precision: str) -> List[str]:
     return flags
 
 
+def source_flags(src: Path) -> List[str]:
+    """nvcc flags the generator asks for in the first lines of a generated source (`// nvcc-flags: ...`), e.g.
+    -prec-div=false: fp32 divisions as reciprocal + multiply (2 ulp) instead of the IEEE sequence with its slow-path call;
+    an IEEE division is ~20 issue slots, the reference's cumulant collision has 22 of them per node."""
+    out: List[str] = []
+    with open(src) as f:
+        for _ in range(6):
+            line = f.readline()
+            if line.startswith("// nvcc-flags:"):
+                out += line.split(":", 1)[1].split()
+    return out
+
+
 def build_model_lib(variant: str, precision: str = "float", force: bool = False, verbose: bool = False) -> Path:
     LIBDIR.mkdir(parents=True, exist_ok=True)
     src = generate_model(variant)
@@ -173,7 +186,7 @@ def build_model_lib(variant: str, precision: str = "float", force: bool = False,
     digest = _hash([src] + hdrs, precision + " ".join(NVCC_FLAGS + ARCH_FLAGS))
     if not force and _stamp_ok(target, digest):
         return target
-    cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
+    cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + source_flags(src) + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
     cmd += precision_flags(precision)
     cmd += ["-o", str(target), str(src), "-lgomp"]
     log = ROOT / "build" / "logs" / f"{variant}_{precision}.ptxas.log"
@@ -243,7 +256,7 @@ def build_custom(modeldef, libname: str, precision: str = "double", extra_flags=
     digest = _hash([src] + hdrs, precision + " ".join(NVCC_FLAGS + ARCH_FLAGS + list(extra_flags)))
     if _stamp_ok(target, digest):
         return target
-    cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + list(extra_flags) + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
+    cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + source_flags(src) + list(extra_flags) + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
     cmd += precision_flags(precision)
     cmd += ["-o", str(target), str(src), "-lgomp"]
     _run(cmd, ROOT / "build" / "logs" / f"{libname}_{precision}.ptxas.log")

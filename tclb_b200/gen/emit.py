@@ -10,6 +10,7 @@ The same node code is compiled for the host as the CPU oracle.
 """
 from __future__ import annotations
 
+import os
 import re
 from pathlib import Path
 from typing import Dict, List
@@ -315,6 +316,10 @@ def emit_model_source(m: ModelDef, libname: str, adjoint: bool = False) -> str:
     L: List[str] = []
     A = L.append
     A(f"// GENERATED by tclb_b200.gen.emit -- model {m.name} ({libname}); do not edit.")
+    # fp32 divisions as reciprocal + multiply unless the model's tuning table (or TCLB_PREC_DIV=1) asks for the IEEE sequence
+    # (measured, 512^3 fp32: reference cumulant files 20.2 -> 25.7 GLUPS, reference d3q19 35.5 -> 38.0, pf_velocity 8.2 -> 9.5)
+    if not (getattr(m, "tuning", {}) or {}).get("prec_div", False) and os.environ.get("TCLB_PREC_DIV", "0") != "1":
+        A("// nvcc-flags: -prec-div=false")
     A('#include <new>\n#include "tclb_node_rt.h"')
     A("#ifdef TCLB_DOUBLE\ntypedef double base_t;\n#define TCLB_REAL_NAME \"double\"\n#else\ntypedef float base_t;\n#define TCLB_REAL_NAME \"float\"\n#endif")
     # adjoint build (-DTCLB_AD, csrc/kernels/tclb_dual.h): the node code computes in dual numbers, memory stays base_t

@@ -87,7 +87,8 @@ def build(options=None, collision="central") -> ModelDef:
     # measured on B200 (profiles/): 64 registers/thread -> 8 blocks of 128 threads per SM is the fastest fp32 build
     # measured on B200 (1024x512x512 fp32): plain kernel 64 regs/8 blocks 28.8 GLUPS (72 regs: 24.9, 80: 23.9);
     # Globals kernel 80 regs/6 blocks 24.3 GLUPS (64 regs: 20.8-23.3, 72: 22.4, 96: 18.9)
-    m.tuning = dict(min_blocks_float=8, min_blocks_double=3, min_blocks_g_float=6)
+    # prec_div: IEEE fp32 division kept (measured: one-block-per-tile kernel 28.0 GLUPS with it, 26.0 without; ring 26.5 / 26.8)
+    m.tuning = dict(min_blocks_float=8, min_blocks_double=3, min_blocks_g_float=6, prec_div=True)
     return m
 
 

@@ -18,7 +18,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIBDIR = os.path.join(ROOT, "tclb_b200", "_lib")
 DEFAULT = ["libtclb_core.so", "libtclb_d3q27_cumulant_float.so", "libtclb_d3q19_float.so", "libtclb_ref_d3q27_pf_velocity_float.so",
-           "libtclb_ref_d3q27_cumulant_float.so", "libtclb_ref_d3q19_float.so", "libtclb_d2q9_float_adjoint.so"]
+           "libtclb_ref_d3q27_cumulant_float.so", "libtclb_ref_d3q19_float.so", "libtclb_d2q9_float_ad.so"]
 WATCH = ["UBLKCP", "SYNCS", "LDGSTS", "UTMALDG", "LDG", "STG", "LDS", "STS", "LDL", "STL", "ATOM", "ATOMG", "RED", "FFMA", "FADD", "FMUL", "DFMA",
          "MUFU", "BAR", "BRA", "SHFL", "NANOSLEEP"]
 

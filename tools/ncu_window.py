@@ -83,6 +83,22 @@ def main():
         d2.iterate(3); d2.sync()
         keep.append(d2)
         todo.append(lambda dd=d2: (dd.iterate(1), dd.sync()))
+    # the four stages of one d3q27_pf_velocity iteration (lowered from the reference's files)
+    try:
+        mp = Model("ref_d3q27_pf_velocity", "float")
+        dp = Domain(mp, (256, 128, 128), "cuda", nranks=1)
+        fl = np.zeros((128, 128, 256), dtype=np.uint32) | mp.flag("MRT")
+        fl[:, 0, :] = mp.flag("Wall"); fl[:, -1, :] = mp.flag("Wall")
+        dp.set_flags(fl)
+        for k, v in (("Density_h", 1.0), ("Density_l", 0.001), ("PhaseField_init", 1.0), ("sigma", 1e-3), ("M", 0.05), ("IntWidth", 4.0),
+                     ("Viscosity_l", 0.16), ("Viscosity_h", 0.16), ("Radius", 30.0), ("CenterX", 128.0), ("CenterY", 64.0), ("CenterZ", 64.0), ("BubbleType", -1.0)):
+            if k in mp.settings or k in mp.zonesettings:
+                dp.set_setting(k, v)
+        dp.init(); dp.iterate(3); dp.sync()
+        keep.append(dp)
+        todo.append(lambda: (dp.iterate(1), dp.sync()))
+    except Exception as e:
+        print("skip ref_d3q27_pf_velocity", e)
     rt.cudaProfilerStart()
     for f in todo:
         f()
