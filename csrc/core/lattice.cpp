@@ -110,13 +110,14 @@ Lattice::~Lattice() {
         if (cuts_dev_) cudaFree(cuts_dev_);
         if (particles_dev_) cudaFree(particles_dev_);
         if (pgrid_dev_) cudaFree(pgrid_dev_);
+        if (ptree_dev_) cudaFree(ptree_dev_);
         if (pgrid_counts_) cudaFree(pgrid_counts_);
         if (pgrid_overflow_) cudaFree(pgrid_overflow_);
         if (st_dev_) cudaFree(st_dev_);
         if (scratch_) cudaFree(scratch_);
         if (pinned_) cudaFreeHost(pinned_);
     } else {
-        free(zone_dev_); free(cuts_dev_); free(st_dev_); free(scratch_); free(particles_dev_); free(pgrid_dev_); free(pgrid_counts_); free(pgrid_overflow_);
+        free(zone_dev_); free(cuts_dev_); free(st_dev_); free(scratch_); free(particles_dev_); free(ptree_dev_); free(pgrid_dev_); free(pgrid_counts_); free(pgrid_overflow_);
     }
 }
 
@@ -173,7 +174,33 @@ void Lattice::set_particles(const std::vector<double> &rows) {
     if (n == 0) return;
     if (rs == 4) { std::vector<float> f(rows.begin(), rows.end()); to_dev(particles_dev_, f.data(), f.size() * 4); }
     else to_dev(particles_dev_, rows.data(), rows.size() * 8);
-    build_particle_grid(rows);
+    ptree_on_ = false;
+    const char *sel = getenv("TCLB_SOLID_CONTAINER");
+    if (sel && !strcmp(sel, "tree")) build_particle_tree(rows);
+    else build_particle_grid(rows);
+}
+std::vector<int> build_particle_tree_words(const std::vector<double> &rows16, int n, double margin);
+// TCLB_SOLID_CONTAINER=tree (the reference's --with-solid-container=tree): threaded box tree, built on the host, walked on the device
+void Lattice::build_particle_tree(const std::vector<double> &rows) {
+    if (model->d->part_margin > 0) part_margin = model->d->part_margin;
+    std::vector<int> words = build_particle_tree_words(rows, n_particles_, part_margin);
+    ptree_nodes_ = (int)(words.size() / 8);
+    if (words.empty()) return;
+    if (words.size() > ptree_cap_) {
+        const size_t cap = words.size() * 2;
+        if (backend == TCLB_BACKEND_CUDA) {
+            TCLB_CUDA(cudaSetDevice(device));
+            sync();
+            if (ptree_dev_) cudaFree(ptree_dev_);
+            TCLB_CUDA(cudaMalloc((void **)&ptree_dev_, cap * sizeof(int)));
+        } else {
+            free(ptree_dev_);
+            ptree_dev_ = (int *)malloc(cap * sizeof(int));
+        }
+        ptree_cap_ = cap;
+    }
+    to_dev(ptree_dev_, words.data(), words.size() * sizeof(int));
+    ptree_on_ = true;
 }
 extern "C" int tclb_particle_grid_fill(const void *rows, int n, int real_size, const double *origin, double inv_delta, const int *gn,
                                        int depth, int *grid, int *counts, int *overflow, int on_device, void *stream);
@@ -512,6 +539,7 @@ void Lattice::fill_launch(tclb_launch_t &L) const {
     L.pgrid = pgrid_on_ ? pgrid_dev_ : nullptr;
     for (int k = 0; k < 3; k++) { L.pg_n[k] = pg_n_[k]; L.pg_origin[k] = pg_origin_[k]; }
     L.pg_depth = pg_depth_; L.pg_inv_delta = pg_inv_delta_;
+    if (ptree_on_) { L.pgrid = ptree_dev_; L.pg_depth = -1; L.pg_n[0] = ptree_nodes_; }      // depth -1: pgrid holds tree nodes
     L.scale = 1.0;
     L.obj_enabled = obj_enabled_ ? 1 : 0;
 }

@@ -170,6 +170,12 @@ class Lattice {
     double pg_origin_[3] = {0, 0, 0}, pg_inv_delta_ = 0;
     bool pgrid_on_ = false;
     void build_particle_grid(const std::vector<double> &rows16);
+    // box tree over the particles (csrc/core/particle_tree.cpp; reference SolidTree), TCLB_SOLID_CONTAINER=tree
+    int *ptree_dev_ = nullptr;
+    size_t ptree_cap_ = 0;
+    int ptree_nodes_ = 0;
+    bool ptree_on_ = false;
+    void build_particle_tree(const std::vector<double> &rows16);
     bool owns_stream_ = false;
     void *pinned_ = nullptr;       // page-locked staging: [0,half) host->device, [half,end) device->host
     size_t pinned_bytes_ = 0;

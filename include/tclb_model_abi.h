@@ -88,7 +88,8 @@ typedef struct {
     int block_x, block_y;
     /* particles: rows of 16 real_t (r, pos, vel, angular vel, force, moment); optional uniform-grid container over them:
      * pgrid = int[pg_n[2]][pg_n[1]][pg_n[0]][pg_depth] particle indices (-1 = empty slot), cell of a position p is
-     * floor((p - pg_origin) * pg_inv_delta) per axis; NULL = look at every particle */
+     * floor((p - pg_origin) * pg_inv_delta) per axis; NULL = look at every particle.  pg_depth == -1: pgrid holds the pg_n[0]
+     * nodes of a threaded box tree instead, 8 words each: float lo[3], hi[3]; int skip; int particle (-1 = inner node) */
     const void *particles; int n_particles;
     const int *pgrid; int pg_n[3]; int pg_depth; double pg_origin[3]; double pg_inv_delta;
     /* CUDA-graph launches: device int[2] = {iteration, epoch} at the start of the graph + this launch's constant offsets */

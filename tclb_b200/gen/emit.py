@@ -174,6 +174,13 @@ struct ParticleS : ParticleI {
 // Range over the particles that can touch the node at (x,y,z): through the uniform-grid container when the runtime built
 // one (reference SolidGrid: the two cells per axis around the node, `depth` slots each), else over every particle
 // (reference SolidAll).  Either way a particle is handed out only if its padded bounding box contains the node.
+TCLB_HD float tclb_word_float(int w) {
+#ifdef __CUDA_ARCH__
+    return __int_as_float(w);
+#else
+    float f; memcpy(&f, &w, 4); return f;
+#endif
+}
 template <class P>
 struct ParticleRange {
     base_t *data;
@@ -185,7 +192,7 @@ struct ParticleRange {
                           const double *org, double inv_delta) : data(data_), n(n_), x(x_), y(y_), z(z_), grid(grid_) {
         gn0 = gn[0]; gn1 = gn[1]; gn2 = gn[2]; depth = depth_;
         lo0 = lo1 = lo2 = hi0 = hi1 = hi2 = 0;
-        if (grid) {
+        if (grid && depth >= 0) {
             const double p[3] = {(double)tclb_value(x), (double)tclb_value(y), (double)tclb_value(z)};
             int lo[3], hi[3];
             for (int k = 0; k < 3; k++) {
@@ -208,6 +215,23 @@ struct ParticleRange {
         int c0, c1, c2, d;     // grid walk: cell and slot
         TCLB_HD void skip() {
             if (!r->grid) { while (i < r->n && !r->near(i)) i++; return; }
+            if (r->depth < 0) {
+                // threaded box tree (csrc/core/particle_tree.cpp): c0 = node to look at next; children follow their parent,
+                // word 6 of a node is where to continue when its subtree is left out
+                const float px = (float)tclb_value(r->x), py = (float)tclb_value(r->y), pz = (float)tclb_value(r->z);
+                while (c0 < r->gn0) {
+                    const int *nd = r->grid + (size_t)c0 * 8;
+                    const bool in = px >= tclb_word_float(nd[0]) && py >= tclb_word_float(nd[1]) && pz >= tclb_word_float(nd[2]) &&
+                                    px <= tclb_word_float(nd[3]) && py <= tclb_word_float(nd[4]) && pz <= tclb_word_float(nd[5]);
+                    if (!in) { c0 = nd[6]; continue; }
+                    const int k = nd[7];
+                    if (k < 0) { c0++; continue; }
+                    c0 = nd[6];
+                    if (r->near(k)) { i = k; return; }
+                }
+                i = r->n;
+                return;
+            }
             for (; c2 <= r->hi2; c2++, c1 = r->lo1) {
                 for (; c1 <= r->hi1; c1++, c0 = r->lo0) {
                     for (; c0 <= r->hi0; c0++, d = 0) {
@@ -223,10 +247,15 @@ struct ParticleRange {
             i = r->n;
         }
         TCLB_HD P operator*() const { return P(r->data + (size_t)i * RFI_DATA_SIZE, r->x, r->y, r->z); }
-        TCLB_HD It &operator++() { if (r->grid) d++; else i++; skip(); return *this; }
+        TCLB_HD It &operator++() { if (!r->grid) i++; else if (r->depth >= 0) d++; skip(); return *this; }
         TCLB_HD bool operator!=(const It &o) const { return i != o.i; }
     };
-    TCLB_HD It begin() const { It it{this, 0, lo0, lo1, lo2, 0}; if (n == 0 || (grid && (lo0 > hi0 || lo1 > hi1 || lo2 > hi2))) it.i = n; else it.skip(); return it; }
+    TCLB_HD It begin() const {
+        It it{this, 0, lo0, lo1, lo2, 0};
+        if (grid && depth < 0) { it.c0 = 0; if (n == 0) it.i = n; else it.skip(); return it; }
+        if (n == 0 || (grid && (lo0 > hi0 || lo1 > hi1 || lo2 > hi2))) it.i = n; else it.skip();
+        return it;
+    }
     TCLB_HD It end() const { return It{this, n, 0, 0, 0, 0}; }
 };
 // the older iterator form of model code: for (ParticleIterator p(X,Y,Z); p; ++p) { ... p.diff ... p.applyForce(f); }

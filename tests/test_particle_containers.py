@@ -63,12 +63,20 @@ def psm_lib(built, reference_dir):
 
 
 @pytest.mark.parametrize("ranks", [1, 2])
-def test_grid_container_equals_scan_over_all_particles_cpu(psm_lib, tclb_bin, tmp_path, ranks):
+@pytest.mark.parametrize("container", ["grid", "tree"])
+def test_containers_equal_scan_over_all_particles_cpu(psm_lib, tclb_bin, tmp_path, ranks, container):
     xml = _case(120, (32, 24, 16), 7, 6)
-    (all_, _), (grid, out) = _run(tclb_bin, tmp_path / "all", "cpu", "all", xml, ranks), _run(tclb_bin, tmp_path / "grid", "cpu", "grid", xml, ranks)
-    _compare(all_, grid, 1e-10)
-    fx = [abs(float(r[8])) for r in grid[0][1:]]
+    (all_, _), (cont, out) = _run(tclb_bin, tmp_path / "all", "cpu", "all", xml, ranks), _run(tclb_bin, tmp_path / container, "cpu", container, xml, ranks)
+    _compare(all_, cont, 1e-10)
+    fx = [abs(float(r[8])) for r in cont[0][1:]]
     assert max(fx) > 1e-4           # the particles do exchange momentum with the fluid
+
+
+def test_tree_with_very_different_radii_cpu(psm_lib, tclb_bin, tmp_path):
+    """two large particles among many small ones: the case the tree exists for (the grid's cells grow with the largest)"""
+    xml = _case(60, (32, 24, 16), 5, 6, rmin=0.8, rmax=1.2).replace("<Periodic", '<Particle x="10" y="12" z="8" r="6.5" log="y"/>\n<Particle x="24" y="10" z="7" r="5.0" vx="0.001" log="y"/>\n<Periodic', 1)
+    (all_, _), (tree, _) = _run(tclb_bin, tmp_path / "all", "cpu", "all", xml), _run(tclb_bin, tmp_path / "tree", "cpu", "tree", xml)
+    _compare(all_, tree, 1e-10)
 
 
 @pytest.mark.gpu
@@ -78,14 +86,16 @@ def test_grid_container_gpu_matches_cpu_and_is_faster_than_the_scan(tclb_bin, tm
     xml = _case(150, (32, 24, 16), 11, 6)
     (cpu, _), (gpu, _) = _run(tclb_bin, tmp_path / "cpu", "cpu", "grid", xml), _run(tclb_bin, tmp_path / "gpu", "gpu", "grid", xml)
     _compare(cpu, gpu, 1e-8)
+    (gtree, _) = _run(tclb_bin, tmp_path / "gpu_tree", "gpu", "tree", xml)
+    _compare(cpu, gtree, 1e-8)
     # 10^4 particles on 128^3: the grid container against the scan over every particle
     import re
     import time
     big = _case(10000, (128, 128, 128), 3, 60, rmin=1.0, rmax=2.0).replace('<Log name="output/forces.csv" Iterations="1"/>', '<Log name="output/forces.csv" Iterations="20"/>').replace('<Log Iterations="2"/>', '<Log Iterations="20"/>')
     t = {}
-    for container in ("grid", "all"):
+    for container in ("grid", "tree", "all"):
         t0 = time.time()
         _run(tclb_bin, tmp_path / f"big_{container}", "gpu", container, big)
         t[container] = time.time() - t0
-    print("10^4 particles, 128^3, 60 iterations: grid %.2f s, all %.2f s" % (t["grid"], t["all"]))
-    assert t["all"] > 3 * t["grid"], t
+    print("10^4 particles, 128^3, 60 iterations: grid %.2f s, tree %.2f s, all %.2f s" % (t["grid"], t["tree"], t["all"]))
+    assert t["all"] > 3 * t["grid"] and t["all"] > 2 * t["tree"], t
