@@ -143,8 +143,13 @@ int tclb_domain_set_field(tclb_domain_h *h, int rank, const char *f, const void 
     int i = h->d->model->find_field(f);
     if (i < 0) fail("unknown field %s", f);
     rank_lat(h, rank)->copy_field_in(i, src);
-    // keep the ghost layers consistent with the new interior (all subdomains in this process: plain copies)
-    if ((int)h->d->local.size() == h->d->dec.nranks) h->d->copy_exchange(rank_lat(h, rank)->cur);
+    // keep the ghost layers consistent with the new interior: plain copies into the neighbours' snapshots (local objects or
+    // mapped peer memory; the other processes must not run before a barrier of the caller), else the exchange hook
+    const int cur = rank_lat(h, rank)->cur;
+    h->d->copy_exchange(cur);
+    bool unwired = false;
+    for (int d = 0; d < TCLB_MAX_NEIGH; d++) if (d != 4 && !rank_lat(h, rank)->halo[d].snap[cur]) unwired = true;
+    if (unwired && h->d->exchange_hook) h->d->exchange_hook(cur);
     GUARD_END_INT
 }
 int tclb_domain_get_quantity(tclb_domain_h *h, int rank, const char *q, const int *b6, void *dst, double scale) {

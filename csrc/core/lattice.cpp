@@ -46,6 +46,10 @@ Lattice::Lattice(Model *m, int backend_, int device_, int rank_, const Box &loca
     gy = m->d->gy; gz = m->d->gz;
     NY = ny + 2 * gy; NZ = nz + 2 * gz;
     plane_elems = (size_t)nx * NY * NZ;
+    // the kernels index one field with 32-bit integers (node index, row offsets, tile numbers)
+    if (plane_elems >= (size_t)1 << 31)
+        fail("subdomain of %d x %d x %d nodes (with ghost layers %zu values per field) exceeds the 2^31 values per field the kernels index; "
+             "use more subdomains (--ranks / more processes)", nx, ny, nz, plane_elems);
     snap_bytes = plane_elems * m->d->n_fields * m->storage_size();
     int s0 = arena_.reserve(snap_bytes, "snapshot0");
     int s1 = arena_.reserve(snap_bytes, "snapshot1");
@@ -854,21 +858,24 @@ void Domain::copy_exchange(int s) {
             if (d == 4) continue;
             int dy = d % 3 - 1, dz = d / 3 - 1;
             if ((dy != 0 && A->gy == 0) || (dz != 0 && A->gz == 0)) continue;
-            int nb = A->halo[d].rank;
-            Lattice *Bl = lat[nb];
-            if (!Bl) continue;      // remote: handled by exchange_hook
+            // the neighbour's snapshot: a local object, or (one process per GPU, direct wiring) its mapped peer memory;
+            // a neighbour reachable only through the exchange hook is left to the hook
+            const HaloTarget &T = A->halo[d];
+            if (!T.snap[s]) continue;
+            const int Bny = T.ny, Bnz = T.nz;
+            const size_t BNY = (size_t)Bny + 2 * A->gy, BNZ = (size_t)Bnz + 2 * A->gz;
             // rows of A that B needs: y in [ny-gy, ny) for dy=+1, [0,gy) for dy=-1, all for 0
             int ys = dy > 0 ? A->ny - A->gy : 0, yn = dy != 0 ? A->gy : A->ny;
             int zs_ = dz > 0 ? A->nz - A->gz : 0, zn = dz != 0 ? A->gz : A->nz;
             for (int f = 0; f < nf; f++)
                 for (int z = 0; z < zn; z++) {
                     int za = zs_ + z;
-                    int zb = dz > 0 ? za - A->nz : (dz < 0 ? za + Bl->nz : za);
+                    int zb = dz > 0 ? za - A->nz : (dz < 0 ? za + Bnz : za);
                     for (int y = 0; y < yn; y++) {
                         int ya = ys + y;
-                        int yb = dy > 0 ? ya - A->ny : (dy < 0 ? ya + Bl->ny : ya);
+                        int yb = dy > 0 ? ya - A->ny : (dy < 0 ? ya + Bny : ya);
                         const char *src = (const char *)A->field_ptr(s, f) + (((size_t)(za + A->gz) * A->NY + (ya + A->gy)) * A->nx) * rs;
-                        char *dst = (char *)Bl->field_ptr(s, f) + (((size_t)(zb + Bl->gz) * Bl->NY + (yb + Bl->gy)) * Bl->nx) * rs;
+                        char *dst = (char *)T.snap[s] + ((size_t)f * (BNY * BNZ * A->nx) + ((size_t)(zb + A->gz) * BNY + (yb + A->gy)) * A->nx) * rs;
                         if (backend == TCLB_BACKEND_CUDA) {
                             if (dy == 0) {   // whole z-plane rows are contiguous in y: one copy per plane
                                 if (y == 0) TCLB_CUDA(cudaMemcpyAsync(dst, src, (size_t)yn * A->nx * rs, cudaMemcpyDefault, (cudaStream_t)A->stream));

@@ -23,7 +23,14 @@ fl = channel_flags(m, shape)
 x0, y0, z0, nx, ny, nz = d.boxes[rank]
 dd.set_local_flags(fl[z0:z0+nz, y0:y0+ny, x0:x0+nx])
 d.set_setting("Viscosity", 0.05); d.set_setting("GravitationX", 1e-5)
-d.init(); d.iterate(30, globals_on_last=True)
+d.init()
+if %(perturb)d:
+    # fields written from the host after initialisation: the neighbours' ghost rows must follow (exchange hook)
+    gx, gy_ = np.meshgrid(np.arange(shape[0]), np.arange(shape[1]))
+    for k, f in enumerate(m.fields[:3]):
+        base = np.zeros((1, shape[1], shape[0])); base[0, y0:y0+ny, x0:x0+nx] = d.get_field(f)[0, y0:y0+ny, x0:x0+nx]
+        d.set_field(f, base * (1.0 + 1e-3 * np.sin(0.3 * gx + 0.2 * gy_ + k))[None])
+d.iterate(30, globals_on_last=True)
 u = np.zeros((ny, nx, 3))
 import ctypes as C
 part = np.zeros((nz, ny, nx, 3)); 
@@ -42,7 +49,7 @@ def test_two_process_gloo_matches_single(tmp_path, built):
     from helpers import run_case
     ref = run_case("d2q9", "double", "cpu", (64, 40, 1), 30)
     script = tmp_path / "w.py"
-    script.write_text(WORKER % dict(root=ROOT, out=str(tmp_path)))
+    script.write_text(WORKER % dict(root=ROOT, out=str(tmp_path), perturb=0))
     env = dict(os.environ, OMP_NUM_THREADS="2")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
                         "--master-port", "29611", str(script)], capture_output=True, text=True, timeout=600, env=env)
@@ -52,6 +59,35 @@ def test_two_process_gloo_matches_single(tmp_path, built):
         x0, y0, z0, nx, ny, nz = np.load(tmp_path / f"box_{rk}.npy")
         u[z0:z0 + nz, y0:y0 + ny, x0:x0 + nx] = np.load(tmp_path / f"u_{rk}.npy")
     assert np.array_equal(u, ref["U"])
+
+
+def test_two_process_set_field_refreshes_neighbour_ghosts(tmp_path, built):
+    from tclb_b200 import build
+    from tclb_b200.runtime import Domain, Model
+    build.build_model_lib("d2q9", "double")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import setup_case
+    m = Model("d2q9", "double")
+    shape = (64, 40, 1)
+    d = Domain(m, shape, "cpu")
+    setup_case(d, m, shape)
+    gx, gy_ = np.meshgrid(np.arange(shape[0]), np.arange(shape[1]))
+    for k, f in enumerate(m.fields[:3]):
+        d.set_field(f, d.get_field(f) * (1.0 + 1e-3 * np.sin(0.3 * gx + 0.2 * gy_ + k))[None])
+    d.iterate(30, globals_on_last=True)
+    ref = d.get_quantity("U")
+    d.close()
+    script = tmp_path / "w.py"
+    script.write_text(WORKER % dict(root=ROOT, out=str(tmp_path), perturb=1))
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29613", str(script)], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    u = np.zeros_like(ref)
+    for rk in range(2):
+        x0, y0, z0, nx, ny, nz = np.load(tmp_path / f"box_{rk}.npy")
+        u[z0:z0 + nz, y0:y0 + ny, x0:x0 + nx] = np.load(tmp_path / f"u_{rk}.npy")
+    assert np.array_equal(u, ref)
 
 
 def test_case_file_on_two_processes_matches_golden_karman(tmp_path, built):
