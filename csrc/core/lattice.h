@@ -185,6 +185,7 @@ class Lattice {
     void *scratch(size_t bytes);
     void to_host(void *dst, const void *src, size_t bytes) const;
     void to_dev(void *dst, const void *src, size_t bytes) const;
+    void pri_stream(const std::string &file, bool save, void *dev_stage, char *host_stage, size_t stage_bytes);
 };
 
 // Decomposition of the global lattice over ranks: y x z split only, the reference's rule

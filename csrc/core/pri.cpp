@@ -6,8 +6,11 @@
 // exists here, produced by a gather (save) / scatter (load) over the slab.
 #include "lattice.h"
 #include "common.h"
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <cuda_runtime.h>
 
 namespace tclb {
 
@@ -81,7 +84,68 @@ static void pri_transfer(const Lattice &L, T *slab, T *image) {
         }
 }
 
+extern "C" int tclb_pri_piece(void *field_dev, void *image_dev, int elem_size, int save, const int *c, const int *th, int X, int Y,
+                              int z0, int nzz, const int *geom, void *stream);
+
+// CUDA backend: the image streams through a fixed device staging buffer and a page-locked host buffer, piece by piece
+// (a 1024x512x512 d3q27 checkpoint is 29 GB; nothing here is larger than the staging buffers).  TCLB_PRI_CHUNK_MB sets
+// their size (default 64).
+void Lattice::pri_stream(const std::string &file, bool save, void *dev_stage, char *host_stage, size_t stage_bytes) {
+    Lattice &L = *this;
+    const int rs = L.model->storage_size();
+    FILE *f = fopen(file.c_str(), save ? "wb" : "rb");
+    if (!f) fail(save ? "cannot write %s" : "cannot read %s", file.c_str());
+    const int geom[6] = {L.nx, L.ny, L.nz, L.gy, L.gz, L.NY};
+    BlockField p;
+    size_t done = 0;
+    for (int m = 0; m < 27; m++)
+        for (int k = 0; k < L.model->d->n_fields; k++) {
+            if (!piece(L, m, k, p)) continue;
+            const int X = p.th[0] * p.ext[0], Y = p.th[1] * p.ext[1], Z = p.th[2] * p.ext[2];
+            const size_t slice = (size_t)X * Y * rs;
+            if (slice > stage_bytes) { fclose(f); fail("checkpoint staging buffer (%zu bytes) is smaller than one z-slice of the lattice (%zu)", stage_bytes, slice); }
+            const int per = (int)std::max<size_t>(1, stage_bytes / slice);
+            char *fld = (char *)L.field_ptr(L.cur, k);
+            for (int z0 = 0; z0 < Z; z0 += per) {
+                const int nzz = std::min(per, Z - z0);
+                const size_t bytes = slice * nzz;
+                if (save) {
+                    if (tclb_pri_piece(fld, dev_stage, rs, 1, p.c, p.th, X, Y, z0, nzz, geom, L.stream) != 0) { fclose(f); fail("checkpoint pack kernel failed"); }
+                    L.to_host(host_stage, dev_stage, bytes);
+                    if (fwrite(host_stage, 1, bytes, f) != bytes) { fclose(f); fail("short write to %s", file.c_str()); }
+                } else {
+                    if (fread(host_stage, 1, bytes, f) != bytes) { fclose(f); fail("%s: size mismatch (expected %zu bytes): the file was written for another model, precision, lattice size or decomposition", file.c_str(), L.pri_bytes()); }
+                    if (p.c[0] == 0) {
+                        L.to_dev(dev_stage, host_stage, bytes);
+                        if (tclb_pri_piece(fld, dev_stage, rs, 0, p.c, p.th, X, Y, z0, nzz, geom, L.stream) != 0) { fclose(f); fail("checkpoint unpack kernel failed"); }
+                        L.sync();
+                    }
+                }
+                done += bytes;
+            }
+        }
+    if (!save) {
+        const int extra = fgetc(f);
+        if (extra != EOF) { fclose(f); fail("%s: size mismatch (expected %zu bytes): the file was written for another model, precision, lattice size or decomposition", file.c_str(), L.pri_bytes()); }
+    }
+    fclose(f);
+    (void)done;
+}
+
 void Lattice::save_pri(const std::string &file) const {
+    if (backend == TCLB_BACKEND_CUDA) {
+        Lattice &self = const_cast<Lattice &>(*this);
+        make_parent_dirs(file);
+        const char *mb = getenv("TCLB_PRI_CHUNK_MB");
+        const size_t stage = (size_t)std::max(1, mb ? atoi(mb) : 64) << 20;
+        void *dev = self.scratch(stage);
+        void *host = nullptr;
+        TCLB_CUDA(cudaSetDevice(device));
+        TCLB_CUDA(cudaHostAlloc(&host, stage, cudaHostAllocDefault));
+        try { self.pri_stream(file, true, dev, (char *)host, stage); } catch (...) { cudaFreeHost(host); throw; }
+        cudaFreeHost(host);
+        return;
+    }
     std::vector<char> slab(snap_bytes), image(pri_bytes());
     to_host(slab.data(), snap_[cur], snap_bytes);
     if (model->storage_size() == 2) pri_transfer<uint16_t, true>(*this, (uint16_t *)slab.data(), (uint16_t *)image.data());
@@ -96,6 +160,17 @@ void Lattice::save_pri(const std::string &file) const {
 }
 
 void Lattice::load_pri(const std::string &file) {
+    if (backend == TCLB_BACKEND_CUDA) {
+        const char *mb = getenv("TCLB_PRI_CHUNK_MB");
+        const size_t stage = (size_t)std::max(1, mb ? atoi(mb) : 64) << 20;
+        void *dev = scratch(stage);
+        void *host = nullptr;
+        TCLB_CUDA(cudaSetDevice(device));
+        TCLB_CUDA(cudaHostAlloc(&host, stage, cudaHostAllocDefault));
+        try { pri_stream(file, false, dev, (char *)host, stage); } catch (...) { cudaFreeHost(host); throw; }
+        cudaFreeHost(host);
+        return;
+    }
     std::vector<char> slab(snap_bytes), image(pri_bytes());
     FILE *f = fopen(file.c_str(), "rb");
     if (!f) fail("cannot read %s", file.c_str());
