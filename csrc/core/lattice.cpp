@@ -410,9 +410,8 @@ void Lattice::copy_field_out_raw(int field, void *dst) const {
     const char *src = (const char *)field_ptr(cur, field);
     if (backend == TCLB_BACKEND_CUDA) {
         TCLB_CUDA(cudaSetDevice(device));
-        for (int z = 0; z < nz; z++)
-            TCLB_CUDA(cudaMemcpyAsync((char *)dst + (size_t)z * ny * nx * rs, src + ((size_t)(z + gz) * NY + gy) * nx * rs,
-                                      (size_t)ny * nx * rs, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+        TCLB_CUDA(cudaMemcpy2DAsync(dst, (size_t)ny * nx * rs, src + ((size_t)gz * NY + gy) * nx * rs, (size_t)NY * nx * rs,
+                                    (size_t)ny * nx * rs, (size_t)nz, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
         TCLB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     } else {
         for (int z = 0; z < nz; z++)
@@ -432,9 +431,9 @@ void Lattice::copy_field_in_raw(int field, const void *srcv) {
     char *dst = (char *)field_ptr(cur, field);
     if (backend == TCLB_BACKEND_CUDA) {
         TCLB_CUDA(cudaSetDevice(device));
-        for (int z = 0; z < nz; z++)
-            TCLB_CUDA(cudaMemcpyAsync(dst + ((size_t)(z + gz) * NY + gy) * nx * rs, (const char *)srcv + (size_t)z * ny * nx * rs,
-                                      (size_t)ny * nx * rs, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+        // the interior of a z-plane is one contiguous run (ny rows of nx): the whole field is ONE pitched copy
+        TCLB_CUDA(cudaMemcpy2DAsync(dst + ((size_t)gz * NY + gy) * nx * rs, (size_t)NY * nx * rs, srcv, (size_t)ny * nx * rs,
+                                    (size_t)ny * nx * rs, (size_t)nz, cudaMemcpyHostToDevice, (cudaStream_t)stream));
         TCLB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     } else {
         for (int z = 0; z < nz; z++)
