@@ -300,85 +300,132 @@ int Solver::write_vtk(const std::string &name, const NameSet &what, const Box &r
 int Solver::write_hdf5(const std::string &name, const NameSet &what, const Box &region_out, bool as_double, bool write_xdmf, bool point_data) {
     logf(L_OUTPUT, "%8d it writing hdf5", iter);
     const tclb_model_t *d = model->d;
-    for (int r = 0; r < opt.nranks; r++)
-        if (!domain->lat[r]) fail("<HDF5> needs every subdomain in this process (run the ranks in one process)");
-    const size_t N = (size_t)region_out.size();
-    H5MinWriter h5;
-    std::string xattr;
-    const std::string file = out_iter_collective_file(name, ".h5");
-    const std::string base = file.substr(file.find_last_of('/') == std::string::npos ? 0 : file.find_last_of('/') + 1);
-    const std::string dims3 = strf("%d %d %d", region_out.nz, region_out.ny, region_out.nx);
-    auto xdmf_attr = [&](const char *fname, int comp, int prec, const char *type) {
-        xattr += strf("      <Attribute Center=\"%s\" %sName=\"%s\">\n        <DataItem DataType=\"%s\" Dimensions=\"%s%s\" Format=\"HDF\" Precision=\"%d\">%s:/%s</DataItem>\n      </Attribute>\n",
-                      point_data ? "Node" : "Cell", comp == 3 ? "AttributeType=\"Vector\" " : "", fname, type, dims3.c_str(), comp == 3 ? " 3" : "", prec, base.c_str(), fname);
-    };
-    // flags of the whole region
-    std::vector<uint32_t> flags(N);
-    auto scatter = [&](int r, const Box &reg, auto &&put) {
-        for (int k = 0; k < reg.nz; k++)
-            for (int j = 0; j < reg.ny; j++)
-                for (int i = 0; i < reg.nx; i++) {
-                    size_t src = ((size_t)k * reg.ny + j) * reg.nx + i;
-                    size_t dst = ((size_t)(k + reg.z0 - region_out.z0) * region_out.ny + (j + reg.y0 - region_out.y0)) * region_out.nx + (i + reg.x0 - region_out.x0);
-                    put(src, dst);
-                }
-        (void)r;
-    };
-    for (int r = 0; r < opt.nranks; r++) {
-        Lattice *l = domain->lat[r];
-        Box reg = domain->dec.boxes[r].intersect(region_out);
-        if (reg.empty()) continue;
-        Box loc = reg; loc.x0 -= l->region.x0; loc.y0 -= l->region.y0; loc.z0 -= l->region.z0;
-        std::vector<uint32_t> fl((size_t)reg.size());
-        l->get_flags(loc, fl.data());
-        scatter(r, reg, [&](size_t s, size_t t) { flags[t] = fl[s]; });
-    }
-    std::vector<unsigned char> small(N);
-    for (int g = 0; g < d->n_nodegroups; g++) {
-        const tclb_nodegroup_t &G = d->nodegroups[g];
-        if (!((what.all && G.save) || what.explicitly_in(G.name))) continue;
-        for (size_t i = 0; i < N; i++) small[i] = (unsigned char)((flags[i] & G.mask) >> G.shift);
-        h5.add(G.name, H5MinWriter::U8, {(uint64_t)region_out.nz, (uint64_t)region_out.ny, (uint64_t)region_out.nx}, small.data());
-        xdmf_attr(G.name, 1, 1, "UChar");
-    }
-    for (int q = 0; q < d->n_quantities; q++) {
-        if (!what.in(d->quantities[q].name)) continue;
-        const double v = units.alt(d->quantities[q].unit);
-        const int comp = d->quantities[q].vector ? 3 : 1;
-        std::vector<double> full(N * comp);
-        for (int r = 0; r < opt.nranks; r++) {
+    // Every subdomain in this process: ONE file of the whole region (what the reference's collective write produces,
+    // src/hdf5Lattice.cpp:154-195).  One process per GPU: every process writes the pieces of its subdomains
+    // (<name>_P<rank>_<iter>.h5) and the process that owns rank 0 writes an XDMF spatial collection over all pieces.
+    bool all_local = true;
+    for (int r = 0; r < opt.nranks; r++) if (!domain->lat[r]) all_local = false;
+    struct PieceOut { Box box; std::string file; };
+    std::vector<PieceOut> pieces;              // what the XDMF index describes
+    std::string xattr_of_piece;                // attribute block with a %s for the file name (same for every piece up to the dims)
+    auto base_of = [](const std::string &file) { return file.substr(file.find_last_of('/') == std::string::npos ? 0 : file.find_last_of('/') + 1); };
+
+    auto write_region = [&](const Box &out, const std::vector<int> &ranks, const std::string &file, std::string &xattr) {
+        const size_t N = (size_t)out.size();
+        H5MinWriter h5;
+        const std::string base = base_of(file);
+        const std::string dims3 = strf("%d %d %d", out.nz, out.ny, out.nx);
+        auto xdmf_attr = [&](const char *fname, int comp, int prec, const char *type) {
+            xattr += strf("      <Attribute Center=\"%s\" %sName=\"%s\">\n        <DataItem DataType=\"%s\" Dimensions=\"%s%s\" Format=\"HDF\" Precision=\"%d\">%s:/%s</DataItem>\n      </Attribute>\n",
+                          point_data ? "Node" : "Cell", comp == 3 ? "AttributeType=\"Vector\" " : "", fname, type, dims3.c_str(), comp == 3 ? " 3" : "", prec, base.c_str(), fname);
+        };
+        auto scatter = [&](const Box &reg, auto &&put) {
+            for (int k = 0; k < reg.nz; k++)
+                for (int j = 0; j < reg.ny; j++)
+                    for (int i = 0; i < reg.nx; i++) {
+                        size_t src = ((size_t)k * reg.ny + j) * reg.nx + i;
+                        size_t dst = ((size_t)(k + reg.z0 - out.z0) * out.ny + (j + reg.y0 - out.y0)) * out.nx + (i + reg.x0 - out.x0);
+                        put(src, dst);
+                    }
+        };
+        std::vector<uint32_t> flags(N);
+        for (int r : ranks) {
             Lattice *l = domain->lat[r];
-            Box reg = domain->dec.boxes[r].intersect(region_out);
+            Box reg = domain->dec.boxes[r].intersect(out);
             if (reg.empty()) continue;
             Box loc = reg; loc.x0 -= l->region.x0; loc.y0 -= l->region.y0; loc.z0 -= l->region.z0;
-            std::vector<char> tmp((size_t)reg.size() * comp * model->real_size());
-            l->get_quantity(q, loc, tmp.data(), 1 / v);
-            scatter(r, reg, [&](size_t s, size_t t) {
-                for (int c = 0; c < comp; c++)
-                    full[t * comp + c] = model->real_size() == 8 ? ((const double *)tmp.data())[s * comp + c] : (double)((const float *)tmp.data())[s * comp + c];
-            });
+            std::vector<uint32_t> fl((size_t)reg.size());
+            l->get_flags(loc, fl.data());
+            scatter(reg, [&](size_t s_, size_t t) { flags[t] = fl[s_]; });
         }
-        std::vector<uint64_t> dims = {(uint64_t)region_out.nz, (uint64_t)region_out.ny, (uint64_t)region_out.nx};
-        if (comp == 3) dims.push_back(3);
-        if (as_double) h5.add(d->quantities[q].name, H5MinWriter::F64, dims, full.data());
-        else { std::vector<float> f32(full.begin(), full.end()); h5.add(d->quantities[q].name, H5MinWriter::F32, dims, f32.data()); }
-        xdmf_attr(d->quantities[q].name, comp, as_double ? 8 : 4, "Float");
+        std::vector<unsigned char> small(N);
+        for (int g = 0; g < d->n_nodegroups; g++) {
+            const tclb_nodegroup_t &G = d->nodegroups[g];
+            if (!((what.all && G.save) || what.explicitly_in(G.name))) continue;
+            for (size_t i = 0; i < N; i++) small[i] = (unsigned char)((flags[i] & G.mask) >> G.shift);
+            h5.add(G.name, H5MinWriter::U8, {(uint64_t)out.nz, (uint64_t)out.ny, (uint64_t)out.nx}, small.data());
+            xdmf_attr(G.name, 1, 1, "UChar");
+        }
+        for (int q = 0; q < d->n_quantities; q++) {
+            if (!what.in(d->quantities[q].name)) continue;
+            const double v = units.alt(d->quantities[q].unit);
+            const int comp = d->quantities[q].vector ? 3 : 1;
+            std::vector<double> full(N * comp);
+            for (int r : ranks) {
+                Lattice *l = domain->lat[r];
+                Box reg = domain->dec.boxes[r].intersect(out);
+                if (reg.empty()) continue;
+                Box loc = reg; loc.x0 -= l->region.x0; loc.y0 -= l->region.y0; loc.z0 -= l->region.z0;
+                std::vector<char> tmp((size_t)reg.size() * comp * model->real_size());
+                l->get_quantity(q, loc, tmp.data(), 1 / v);
+                scatter(reg, [&](size_t s_, size_t t) {
+                    for (int c = 0; c < comp; c++)
+                        full[t * comp + c] = model->real_size() == 8 ? ((const double *)tmp.data())[s_ * comp + c] : (double)((const float *)tmp.data())[s_ * comp + c];
+                });
+            }
+            std::vector<uint64_t> dims = {(uint64_t)out.nz, (uint64_t)out.ny, (uint64_t)out.nx};
+            if (comp == 3) dims.push_back(3);
+            if (as_double) h5.add(d->quantities[q].name, H5MinWriter::F64, dims, full.data());
+            else { std::vector<float> f32(full.begin(), full.end()); h5.add(d->quantities[q].name, H5MinWriter::F32, dims, f32.data()); }
+            xdmf_attr(d->quantities[q].name, comp, as_double ? 8 : 4, "Float");
+        }
+        h5.write(file);
+    };
+
+    std::vector<std::string> xattrs;
+    if (all_local) {
+        std::vector<int> ranks;
+        for (int r = 0; r < opt.nranks; r++) ranks.push_back(r);
+        const std::string file = out_iter_collective_file(name, ".h5");
+        std::string xa;
+        write_region(region_out, ranks, file, xa);
+        pieces.push_back({region_out, file});
+        xattrs.push_back(xa);
+    } else {
+        for (int r = 0; r < opt.nranks; r++) {
+            Box reg = domain->dec.boxes[r].intersect(region_out);
+            if (reg.empty()) continue;
+            const std::string file = out_iter_file(name, ".h5", r);
+            std::string xa;
+            if (domain->lat[r]) write_region(reg, {r}, file, xa);
+            pieces.push_back({reg, file});
+            xattrs.push_back(xa);
+        }
+        // the attribute blocks of pieces written elsewhere: same text as a local piece with that piece's dims and file name
+        std::string pattern, pat_dims, pat_file;
+        for (size_t k = 0; k < pieces.size(); k++)
+            if (!xattrs[k].empty()) { pattern = xattrs[k]; pat_dims = strf("%d %d %d", pieces[k].box.nz, pieces[k].box.ny, pieces[k].box.nx); pat_file = base_of(pieces[k].file); break; }
+        auto replace_all = [](std::string t, const std::string &a, const std::string &b) {
+            for (size_t at = 0; (at = t.find(a, at)) != std::string::npos; at += b.size()) t.replace(at, a.size(), b);
+            return t;
+        };
+        for (size_t k = 0; k < pieces.size(); k++)
+            if (xattrs[k].empty() && !pattern.empty())
+                xattrs[k] = replace_all(replace_all(pattern, "Dimensions=\"" + pat_dims, "Dimensions=\"" + strf("%d %d %d", pieces[k].box.nz, pieces[k].box.ny, pieces[k].box.nx)),
+                                        pat_file + ":/", base_of(pieces[k].file) + ":/");
     }
-    h5.write(file);
-    if (write_xdmf) {
+    if (write_xdmf && domain->lat[0]) {
         const double m = units.alt("1m"), sec = units.alt("1s"), shift = point_data ? 0.5 : 0.0;
         const std::string xf = out_iter_collective_file(name, ".xmf");
         FILE *f = fopen(xf.c_str(), "w");
         if (!f) fail("cannot write %s", xf.c_str());
-        fprintf(f, "<?xml version=\"1.0\"?>\n<Xdmf xmlns:xi=\"http://www.w3.org/2001/XInclude\" Version=\"3.0\">\n  <Domain>\n    <Grid Name=\"Lattice\">\n");
-        fprintf(f, "      <Time Value=\"%.15g\"/>\n", iter / sec);
-        fprintf(f, "      <Geometry Origin=\"\" Type=\"ORIGIN_DXDYDZ\">\n        <DataItem DataType=\"Float\" Dimensions=\"3\" Format=\"XML\" Precision=\"8\">%.15g %.15g %.15g</DataItem>\n",
-                (pz + shift + region_out.z0) / m, (py + shift + region_out.y0) / m, (px + shift + region_out.x0) / m);
-        fprintf(f, "        <DataItem DataType=\"Float\" Dimensions=\"3\" Format=\"XML\" Precision=\"8\">%.15g %.15g %.15g</DataItem>\n      </Geometry>\n", 1 / m, 1 / m, 1 / m);
-        if (point_data) fprintf(f, "      <Topology Dimensions=\"%s\" Type=\"3DCoRectMesh\"/>\n", dims3.c_str());
-        else fprintf(f, "      <Topology Dimensions=\"%d %d %d\" Type=\"3DCoRectMesh\"/>\n", region_out.nz + 1, region_out.ny + 1, region_out.nx + 1);
-        fputs(xattr.c_str(), f);
-        fprintf(f, "    </Grid>\n  </Domain>\n</Xdmf>\n");
+        fprintf(f, "<?xml version=\"1.0\"?>\n<Xdmf xmlns:xi=\"http://www.w3.org/2001/XInclude\" Version=\"3.0\">\n  <Domain>\n");
+        const bool coll = pieces.size() > 1 || !all_local;
+        if (coll) fprintf(f, "    <Grid Name=\"Lattice\" GridType=\"Collection\" CollectionType=\"Spatial\">\n      <Time Value=\"%.15g\"/>\n", iter / sec);
+        for (size_t k = 0; k < pieces.size(); k++) {
+            const Box &b = pieces[k].box;
+            if (coll) fprintf(f, "    <Grid Name=\"Lattice_P%02zu\">\n", k);
+            else fprintf(f, "    <Grid Name=\"Lattice\">\n      <Time Value=\"%.15g\"/>\n", iter / sec);
+            fprintf(f, "      <Geometry Origin=\"\" Type=\"ORIGIN_DXDYDZ\">\n        <DataItem DataType=\"Float\" Dimensions=\"3\" Format=\"XML\" Precision=\"8\">%.15g %.15g %.15g</DataItem>\n",
+                    (pz + shift + b.z0) / m, (py + shift + b.y0) / m, (px + shift + b.x0) / m);
+            fprintf(f, "        <DataItem DataType=\"Float\" Dimensions=\"3\" Format=\"XML\" Precision=\"8\">%.15g %.15g %.15g</DataItem>\n      </Geometry>\n", 1 / m, 1 / m, 1 / m);
+            if (point_data) fprintf(f, "      <Topology Dimensions=\"%d %d %d\" Type=\"3DCoRectMesh\"/>\n", b.nz, b.ny, b.nx);
+            else fprintf(f, "      <Topology Dimensions=\"%d %d %d\" Type=\"3DCoRectMesh\"/>\n", b.nz + 1, b.ny + 1, b.nx + 1);
+            fputs(xattrs[k].c_str(), f);
+            fprintf(f, "    </Grid>\n");
+        }
+        if (coll) fprintf(f, "    </Grid>\n");
+        fprintf(f, "  </Domain>\n</Xdmf>\n");
         fclose(f);
     }
     return 0;

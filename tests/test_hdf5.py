@@ -29,3 +29,31 @@ def test_hdf5_output_matches_vtk_fields(tclb_bin, tmp_path):
     assert txt.size > 0
     x = open(xmf).read()
     assert 'Type="3DCoRectMesh"' in x and "k_HDF5_00000050.h5:/U" in x and re.search(r'Dimensions="1 100 1024 3"', x)
+
+
+def test_hdf5_pieces_from_two_processes(tmp_path):
+    """One process per subdomain: every process writes its piece, rank 0 the XDMF spatial collection; the pieces put together
+    equal the single-file output of the one-process run (reference: collective write, src/hdf5Lattice.cpp:154-195)."""
+    import sys
+    from tclb_b200 import build
+    from tclb_b200.utils import h5min
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    build.build_model_lib("d2q9", "double")
+    xml = KARMAN_XML.replace('<Solve Iterations="1000"', '<HDF5 Iterations="50" what="U,Rho,BOUNDARY" precision="double"/><Solve Iterations="50"')
+    one, two = tmp_path / "one", tmp_path / "two"
+    one.mkdir(); two.mkdir()
+    (one / "k.xml").write_text(xml); (two / "k.xml").write_text(xml)
+    env = dict(os.environ, OMP_NUM_THREADS="2", PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    r = subprocess.run([sys.executable, "-m", "tclb_b200.run", "--cpu", "--precision", "double", "--ranks", "2", "d2q9", "k.xml"], cwd=one, capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port", "29641",
+                        "-m", "tclb_b200.run", "--cpu", "--precision", "double", "d2q9", "k.xml"], cwd=two, capture_output=True, text=True, env=env, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    whole = h5min.read(str(one / "output" / "k_HDF5_00000050.h5"))
+    p0 = h5min.read(str(two / "output" / "k_HDF5_P00_00000050.h5"))
+    p1 = h5min.read(str(two / "output" / "k_HDF5_P01_00000050.h5"))
+    for name in ("U", "Rho", "BOUNDARY"):
+        assert np.array_equal(np.concatenate([p0[name], p1[name]], axis=1), whole[name]), name
+    x = open(two / "output" / "k_HDF5_00000050.xmf").read()
+    assert 'CollectionType="Spatial"' in x and "k_HDF5_P00_00000050.h5:/U" in x and "k_HDF5_P01_00000050.h5:/Rho" in x
+    assert x.count("<Grid Name=\"Lattice_P") == 2 and x.count('Dimensions="1 50 1024 3"') == 2
