@@ -184,19 +184,37 @@ TCLB_REGISTER_HANDLER("Adjoint", AcAdjoint)
 // <Objective Drag="1" PressureLoss="-0.5"/>: weights of SUM Globals in the objective (sets <Global>InObj in every zone)
 class AcObjective : public Action {
   public:
+    // <Objective NAME="weight" .../>: NAME is a Global or an objective the model declared with AddObjective (an expression
+    // of the Globals).  The weighted objectives are linearised at the CURRENT values of the Globals: the zonal settings
+    // <Global>InObj become sum_k weight_k * d(objective_k)/d(Global), and the Objective global their weighted sum
+    // (reference src/Handlers/acObjective.cpp:4-38, generated OF_<name> functions src/Lists.cpp.Rt:17-34).
     int init() override {
         Action::init();
         const tclb_model_t *d = solver->model->d;
+        const int n = d->n_globals;
+        std::vector<double> glob(n), grad(n), in_obj(n, 0.0);
+        for (int g = 0; g < n; g++) glob[g] = solver->domain->globals[g];
+        double obj = 0;
         int nset = 0;
-        for (int g = 0; g < d->sum_globals; g++) {
-            std::string nm = d->globals[g].name;
-            if (nm == "Objective") continue;
-            const double w = node->has_attr(nm) ? atof(node->attr(nm).c_str()) : 0.0;
-            if (solver->model->find_zonesetting(nm + "InObj") < 0) continue;
-            solver->set_param(nm + "InObj", node->has_attr(nm) ? node->attr(nm) : "0", "", true, "");
+        for (int k = 0; k < d->n_objectives; k++) {
+            const std::string nm = d->objectives[k].name;
+            if (nm == "Objective" || !node->has_attr(nm)) continue;
+            const double w = atof(node->attr(nm).c_str());
+            double val = 0;
+            std::fill(grad.begin(), grad.end(), 0.0);
+            d->objectives[k].fun(glob.data(), &val, grad.data());
+            obj += w * val;
+            for (int g = 0; g < n; g++) in_obj[g] += w * grad[g];
             if (w != 0.0) nset++;
         }
-        if (nset == 0) logf(L_WARNING, "<Objective> names no Global of this model: the objective is zero");
+        for (int g = 0; g < d->sum_globals; g++) {
+            const std::string nm = d->globals[g].name;
+            if (nm == "Objective" || solver->model->find_zonesetting(nm + "InObj") < 0) continue;
+            solver->set_param(nm + "InObj", strf("%.17g", in_obj[g]), "", true, "");
+        }
+        const int oi = objective_index(solver);
+        if (oi >= 0) solver->domain->globals[oi] = obj;
+        if (nset == 0) logf(L_WARNING, "<Objective> names no objective of this model: the objective is zero");
         return 0;
     }
 };

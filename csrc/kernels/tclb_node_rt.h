@@ -26,6 +26,7 @@ struct uchar4 { unsigned char x, y, z, w; };
 template <class T> struct tclb_vec3 { T x, y, z; };
 
 // value part of a scalar (the adjoint build adds an overload for dual numbers, tclb_dual.h)
+TCLB_HD int tclb_value(int x) { return x; }
 TCLB_HD float tclb_value(float x) { return x; }
 TCLB_HD double tclb_value(double x) { return x; }
 

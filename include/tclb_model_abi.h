@@ -12,7 +12,7 @@
 extern "C" {
 #endif
 
-#define TCLB_ABI_VERSION 10
+#define TCLB_ABI_VERSION 11
 #define TCLB_MAX_NEIGH 9            /* (dy,dz) in {-1,0,1}^2 ; x is never decomposed */
 #define TCLB_MAX_RANKS 16           /* subdomains that exchange Globals through peer memory (one box) */
 #define TCLB_GL_RING 8              /* depth of the Globals publication ring */
@@ -37,6 +37,9 @@ typedef struct { const char *name, *main; int particle;
                  const unsigned char *load_density, *save_field, *read_field; } tclb_stage_t;
 typedef struct { const char *name; int n_stages; const int *stages; } tclb_action_t;
 typedef struct { const char *name; int value; } tclb_option_t;
+/* objective = expression of the Globals (reference AddObjective, src/conf.R:349-372; every Global is one by default):
+ * value and gradient with respect to every Global at the given values (src/Lists.cpp.Rt:17-34 OF_<name>) */
+typedef struct { const char *name; void (*fun)(const double *glob, double *obj, double *grad); } tclb_objective_t;
 
 /* Synthetic-turbulence mode set (reference src/SyntheticTurbulence.h:20-110) */
 typedef struct { double k[3]; double a[3]; double b[3]; double freq; } tclb_st_mode_t;
@@ -125,6 +128,7 @@ typedef struct {
     const char *storage_name;
     const double *field_shift;
     double part_margin;                  /* reach of a particle beyond its radius in the particle stages (model's PartMargin) */
+    int n_objectives; const tclb_objective_t *objectives;
 } tclb_model_t;
 
 /* every model library exports exactly this symbol */

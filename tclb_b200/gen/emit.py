@@ -701,6 +701,9 @@ struct Node {
     TCLB_HD real_t load_field(int fi, int dx, int dy, int dz) const { return load_field_plain(fi, dx, dy, dz); }
 #endif
     TCLB_HD real_t load_field(int fi, int dx, int dy) const { return load_field(fi, dx, dy, 0); }
+    // offsets computed in the arithmetic type (e.g. a wall normal): truncated like the implicit conversion of the primal build
+    template <class A_, class B_, class C_>
+    TCLB_HD real_t load_field(int fi, A_ dx, B_ dy, C_ dz) const { return load_field(fi, (int)tclb_value(dx), (int)tclb_value(dy), (int)tclb_value(dz)); }
     template <class P> TCLB_HD ParticleRange<P> particle_range(real_t x, real_t y, real_t z) const {
         return ParticleRange<P>(ka_.particles, ka_.n_particles, x, y, z, ka_.pgrid, ka_.pg_n, ka_.pg_depth, ka_.pg_origin, ka_.pg_inv_delta);
     }
@@ -1099,6 +1102,28 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     for k, v in m.options.items():
         A(f"    {{{_cstr(k)}, {int(v)}}},")
     A("    {0, 0}};")
+    # objectives: every Global by name, plus the model's AddObjective expressions of the Globals
+    from .poly import Poly as _Poly, to_c as _to_c
+    objs = {g.name: _Poly.sym(g.name) for g in m.globals}
+    for k, v in (getattr(m, "objectives", {}) or {}).items():
+        objs[k] = _Poly.lift(v[0] if hasattr(v, "__len__") and not isinstance(v, (str, _Poly)) else v)
+    gnames = [g.name for g in m.globals]
+    for k, e in objs.items():
+        used = sorted({s_ for mono in e.t for s_, _ in mono})
+        bad = [u for u in used if u not in gnames]
+        if bad:
+            raise ValueError(f"objective {k} uses {bad}, which are not Globals of the model")
+        A(f"static void OF_{k}(const double *glob, double *obj, double *grad) {{")
+        for u in used:
+            A(f"    const double {u} = glob[{gnames.index(u)}];")
+        A(f"    obj[0] = {_to_c(e)};")
+        for gi, gname in enumerate(gnames):
+            A(f"    grad[{gi}] = {_to_c(e.deriv(gname))};")
+        A("}")
+    A("const tclb_objective_t t_objectives[] = {")
+    for k in objs:
+        A(f"    {{{_cstr(k)}, OF_{k}}},")
+    A("    {0, 0}};")
     A(f"""
 const tclb_model_t t_model = {{
     TCLB_ABI_VERSION, {_cstr(libname)}, {_cstr(m.name)}, (int)sizeof(real_t), (int)sizeof(flag_t),
@@ -1110,7 +1135,8 @@ const tclb_model_t t_model = {{
     GY, GZ,
     run_stage_impl, get_quantity_impl, color_impl, kernel_info_impl, last_error_impl,
     (int)sizeof(storage_t), TCLB_STORAGE_SHIFTED, TCLB_STORAGE_NAME, t_field_shift,
-    (double)PART_MAR_VALUE
+    (double)PART_MAR_VALUE,
+    {len(objs)}, t_objectives
 }};
 }}  // namespace
 extern "C" const tclb_model_t *tclb_get_model(void) {{ return &t_model; }}

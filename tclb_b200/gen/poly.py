@@ -76,6 +76,22 @@ class Poly:
             x = x.item()
         return Poly.const(x)
 
+    def deriv(self, var: str) -> "Poly":
+        """partial derivative with respect to one symbol (Laurent exponents allowed)"""
+        out: Dict[Mono, Number] = {}
+        for m, c in self.t.items():
+            d = dict(m)
+            e = d.get(var, 0)
+            if e == 0:
+                continue
+            if e == 1:
+                d.pop(var)
+            else:
+                d[var] = e - 1
+            key = tuple(sorted(d.items()))
+            out[key] = out.get(key, 0) + c * e
+        return Poly(out)
+
     # -- queries ------------------------------------------------------------------------
     def is_zero(self) -> bool:
         return not self.t

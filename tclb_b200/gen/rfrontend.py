@@ -13,6 +13,7 @@ from typing import Dict, List, Optional
 import numpy as np
 
 from .modeldef import ModelDef
+from .poly import Poly, PVec
 from .rinterp import Env, Interp
 from .rlang import NA, NULL, DataFrame, RError, RList, scalar, vec
 
@@ -211,7 +212,18 @@ def load_dynamics_r(model_dir: str, name: Optional[str] = None, options: Optiona
     env.set("AddNodeType", wrap(m.AddNodeType))
     env.set("AddDescription", wrap(m.AddDescription))
     env.set("AddAction", wrap(m.AddAction))
-    env.set("AddObjective", lambda I_, a, k: NULL)
+    def add_objective(I_, a, k):
+        name = _pyval(a[0] if a else k["name"])
+        expr = a[1] if len(a) > 1 else k["expr"]
+        if isinstance(expr, PVec):
+            if len(expr) != 1:
+                raise RError("Only one expression for an objective in AddObjective")
+            expr = expr[0]
+        if not isinstance(expr, Poly):
+            raise RError("Objective need to be a polyAlgebra expression")
+        m.AddObjective(str(name), expr)
+        return NULL
+    env.set("AddObjective", add_objective)
     env.set("SetOptions", wrap(m.SetOptions, {"permissive.access": "permissive_access"}))
 
     def add_stage(I_, a, k):

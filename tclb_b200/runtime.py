@@ -69,6 +69,10 @@ class _Option(C.Structure):
     _fields_ = [("name", C.c_char_p), ("value", C.c_int)]
 
 
+class _Objective(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("fun", C.CFUNCTYPE(None, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)))]
+
+
 class _ModelDesc(C.Structure):
     _fields_ = [("abi_version", C.c_int), ("name", C.c_char_p), ("base_name", C.c_char_p),
                 ("real_size", C.c_int), ("flag_size", C.c_int),
@@ -88,7 +92,8 @@ class _ModelDesc(C.Structure):
                 ("run_stage", C.c_void_p), ("get_quantity", C.c_void_p), ("color", C.c_void_p),
                 ("kernel_info", C.c_void_p), ("last_error", C.c_void_p),
                 ("storage_size", C.c_int), ("storage_shifted", C.c_int), ("storage_name", C.c_char_p),
-                ("field_shift", C.POINTER(C.c_double))]
+                ("field_shift", C.POINTER(C.c_double)), ("part_margin", C.c_double),
+                ("n_objectives", C.c_int), ("objectives", C.POINTER(_Objective))]
 
 
 _core = None
@@ -230,6 +235,7 @@ class Model:
         self.setting_defaults = {_s(d.settings[i].name): _s(d.settings[i].default_value) for i in range(d.n_settings)}
         self.setting_defaults.update({_s(d.zonesettings[i].name): _s(d.zonesettings[i].default_value)
                                       for i in range(d.n_zonesettings)})
+        self.objectives = [_s(d.objectives[i].name) for i in range(d.n_objectives)]
         self.zone_shift, self.zone_max = int(d.zone_shift), int(d.zone_max)
         self.storage = _s(d.storage_name)
         self.field_shift = [float(d.field_shift[i]) if d.storage_shifted else 0.0 for i in range(d.n_fields)]
@@ -256,6 +262,15 @@ class Model:
             per_stage.append({"stage": _s(st.name), "fields_read": len(rd), "fields_written": len(wr), "bytes": b})
             total += b
         return {"action": action, "bytes_per_update": total, "stages": per_stage}
+
+    def objective(self, name: str, globals_values) -> tuple:
+        """(value, gradient with respect to every Global) of a model objective at the given values of the Globals"""
+        k = self.objectives.index(name)
+        n = len(self.globals)
+        g = (C.c_double * n)(*[float(globals_values[x]) if isinstance(globals_values, dict) else float(globals_values[i]) for i, x in enumerate(self.globals)])
+        val, grad = (C.c_double * 1)(), (C.c_double * n)()
+        self.d.objectives[k].fun(g, val, grad)
+        return float(val[0]), np.array(list(grad))
 
     def flag(self, *names: str) -> int:
         v = 0
