@@ -299,28 +299,34 @@ void *Lattice::field_ptr(int snap, int field) const {
 }
 
 // ---- flags -------------------------------------------------------------------------------
+// Flags of a box: only the z-planes the box touches travel (they are one contiguous run of the slab), not the whole array.
 void Lattice::flag_overwrite(const uint32_t *fl, const Box &b) {
+    if (b.nx <= 0 || b.ny <= 0 || b.nz <= 0) return;
     const int fs = model->flag_size();
-    std::vector<unsigned char> host(plane_elems * fs);
-    to_host(host.data(), flags_, host.size());
+    const size_t plane = (size_t)NY * nx, first = (size_t)(b.z0 + gz) * plane;
+    std::vector<unsigned char> host((size_t)b.nz * plane * fs);
+    const bool whole_rows = b.x0 == 0 && b.nx == nx && b.y0 == 0 && b.ny == ny && gy == 0;
+    if (!whole_rows) to_host(host.data(), (const char *)flags_ + first * fs, host.size());     // keep what the box does not cover
     for (int z = 0; z < b.nz; z++)
         for (int y = 0; y < b.ny; y++)
             for (int x = 0; x < b.nx; x++) {
-                size_t i = ((size_t)(z + b.z0 + gz) * NY + (y + b.y0 + gy)) * nx + (x + b.x0);
+                size_t i = ((size_t)z * NY + (y + b.y0 + gy)) * nx + (x + b.x0);
                 uint32_t v = fl[((size_t)z * b.ny + y) * b.nx + x];
                 if (fs == 2) ((uint16_t *)host.data())[i] = (uint16_t)v;
                 else ((uint32_t *)host.data())[i] = v;
             }
-    to_dev(flags_, host.data(), host.size());
+    to_dev((char *)flags_ + first * fs, host.data(), host.size());
 }
 void Lattice::get_flags(const Box &b, uint32_t *out) const {
+    if (b.nx <= 0 || b.ny <= 0 || b.nz <= 0) return;
     const int fs = model->flag_size();
-    std::vector<unsigned char> host(plane_elems * fs);
-    to_host(host.data(), flags_, host.size());
+    const size_t plane = (size_t)NY * nx, first = (size_t)(b.z0 + gz) * plane;
+    std::vector<unsigned char> host((size_t)b.nz * plane * fs);
+    to_host(host.data(), (const char *)flags_ + first * fs, host.size());
     for (int z = 0; z < b.nz; z++)
         for (int y = 0; y < b.ny; y++)
             for (int x = 0; x < b.nx; x++) {
-                size_t i = ((size_t)(z + b.z0 + gz) * NY + (y + b.y0 + gy)) * nx + (x + b.x0);
+                size_t i = ((size_t)z * NY + (y + b.y0 + gy)) * nx + (x + b.x0);
                 out[((size_t)z * b.ny + y) * b.nx + x] = fs == 2 ? ((uint16_t *)host.data())[i] : ((uint32_t *)host.data())[i];
             }
 }
