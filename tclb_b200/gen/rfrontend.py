@@ -278,4 +278,21 @@ def load_model(model_dir: str, name: Optional[str] = None, options: Optional[Dic
     else:
         m.code = rtemplate._read(os.path.join(model_dir, "Dynamics.c"))
     m.finalize()
+    if not getattr(m, "tuning", None):
+        m.tuning = dict(DIRECTORY_TUNING.get(m.name, {}))
+        tj = os.path.join(model_dir, "tuning.json")
+        if os.path.exists(tj):
+            import json
+            m.tuning.update(json.load(open(tj)))
     return m
+
+
+# Occupancy hints for model directories, by model name (what the native models carry in their own `tuning`): resident
+# blocks per SM the one-block-per-tile kernel is compiled for.  Measured on B200, 512^3 fp32, no Globals
+# (profiles/r2/ref_lowered_occupancy.txt): d3q27_cumulant 71 registers/7 blocks 25.6 GLUPS -> 64/8 28.2; d3q19 56/9 38.0 ->
+# 48/10 40.1.  A directory can override this with a `tuning.json` next to its Dynamics.R.
+DIRECTORY_TUNING: Dict[str, Dict[str, int]] = {
+    "d3q27_cumulant": {"min_blocks_float": 8},
+    "d3q19": {"min_blocks_float": 10},
+}
+
