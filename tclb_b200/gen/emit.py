@@ -882,6 +882,13 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
         A(f"constexpr int RING_ROWS_{si} = {len(ld) if ok else 0}, RING_EDGES_{si} = {len(edges) if ok else 0};")
         A(f"constexpr int RING_BYTES_{si} = RING_ROWS_{si} * RING_ROW + TCLB_TILE_X * (int)sizeof(flag_t);")
         A(f"constexpr bool RING_OK_{si} = {'true' if ok else 'false'} && sizeof(storage_t) >= 4;")
+        # chosen by default (launches with Globals) only where it was measured to win: stages that pull one lattice of up to
+        # 32 densities and read nothing through stencil accessors (d3q27_pf_velocity's 50-density stages run 8.2 GLUPS with
+        # one block per tile and 5.5 with the ring)
+        pulled = {d.field for _, d in ld}
+        stencil = any(bool(f.read.get(s_.name)) and f.name not in pulled and any((f.minx, f.maxx, f.miny, f.maxy, f.minz, f.maxz))
+                      for f in m.fields)
+        A(f"constexpr bool RING_DEFAULT_{si} = RING_OK_{si} && {'true' if (ok and len(ld) <= 32 and not stencil) else 'false'};")
         A(f"template <int GMODE> TCLB_D void load_stage_ring_{si}(Node<GMODE> &n, const unsigned char *sb, int t) {{")
         if ok:
             for k, (di, d) in enumerate(ld):
@@ -938,6 +945,7 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
         A(f"    if (S == {si}) ring_issue_edges_{si}(a, sb, lane, row0, x0);")
     A("}")
     A("template <int S> constexpr bool ring_ok() { return " + " || ".join(f"(S == {si} && RING_OK_{si} && RING_BYTES_{si} * TCLB_RING_SLOTS <= 100 * 1024)" for si in range(len(m.stages))) + "; }")
+    A("template <int S> constexpr bool ring_default() { return ring_ok<S>() && (" + " || ".join(f"(S == {si} && RING_DEFAULT_{si})" for si in range(len(m.stages))) + "); }")
     A("template <int S> constexpr int ring_bytes() { return " + " + ".join(f"(S == {si} ? RING_BYTES_{si} : 0)" for si in range(len(m.stages))) + "; }")
     A("#endif")
     A("template <int GMODE> TCLB_HD void load_all(Node<GMODE> &n, const KArgs &a, int x, int i0, int im, int ip) {")
