@@ -882,13 +882,11 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
         A(f"constexpr int RING_ROWS_{si} = {len(ld) if ok else 0}, RING_EDGES_{si} = {len(edges) if ok else 0};")
         A(f"constexpr int RING_BYTES_{si} = RING_ROWS_{si} * RING_ROW + TCLB_TILE_X * (int)sizeof(flag_t);")
         A(f"constexpr bool RING_OK_{si} = {'true' if ok else 'false'} && sizeof(storage_t) >= 4;")
-        # chosen by default (launches with Globals) only where it was measured to win: stages that pull one lattice of up to
-        # 32 densities and read nothing through stencil accessors (d3q27_pf_velocity's 50-density stages run 8.2 GLUPS with
-        # one block per tile and 5.5 with the ring)
-        pulled = {d.field for _, d in ld}
-        stencil = any(bool(f.read.get(s_.name)) and f.name not in pulled and any((f.minx, f.maxx, f.miny, f.maxy, f.minz, f.maxz))
-                      for f in m.fields)
-        A(f"constexpr bool RING_DEFAULT_{si} = RING_OK_{si} && {'true' if (ok and len(ld) <= 32 and not stencil) else 'false'};")
+        # chosen by default (launches with Globals) only where it was measured to win (512^3 fp32, Globals every iteration,
+        # one block per tile -> ring): d3q27_cumulant 24.1 -> 26.9 GLUPS, d3q27_cumulant_AVG (34 densities) 13.4 -> 16.9, d3q19
+        # 32.5 -> 37.4; it loses on small velocity sets (d2q9_bc 72.5 -> 55.9, d2q9_kuper 20.6 -> 17.0: too little arithmetic
+        # per tile to hide the ring's bookkeeping) and on d3q27_pf_velocity's 50-density stages (8.2 -> 5.5)
+        A(f"constexpr bool RING_DEFAULT_{si} = RING_OK_{si} && {'true' if (ok and 15 <= len(ld) <= 40) else 'false'};")
         A(f"template <int GMODE> TCLB_D void load_stage_ring_{si}(Node<GMODE> &n, const unsigned char *sb, int t) {{")
         if ok:
             for k, (di, d) in enumerate(ld):
