@@ -57,9 +57,9 @@ def d2q9_libs(built):
     build.build_adjoint_lib("d2q9", "double")
 
 
-def _run(tclb_bin, tmp_path, model, xml, timeout=600):
+def _run(tclb_bin, tmp_path, model, xml, timeout=600, backend="cpu"):
     (tmp_path / "case.xml").write_text(xml)
-    r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", model, "case.xml"], cwd=tmp_path, capture_output=True, text=True, timeout=timeout)
+    r = subprocess.run([tclb_bin, f"--{backend}", "--precision", "double", model, "case.xml"], cwd=tmp_path, capture_output=True, text=True, timeout=timeout)
     out = r.stdout + r.stderr
     assert r.returncode == 0, out[-4000:]
     return out
@@ -141,3 +141,26 @@ def test_field_designs_pass_fdtest(reference_dir, tclb_bin, tmp_path, name, desi
         ev = [float(v) for v in re.findall(r"Optimize: evaluation \d+ objective ([-+.eE0-9]+)", out)]
         best = float(re.search(r"Optimize: best objective ([-+.eE0-9]+)", out).group(1))
         assert len(ev) >= 3 and best >= ev[0]
+
+
+@pytest.mark.gpu
+def test_designs_pass_fdtest_on_the_gpu(tclb_bin, tmp_path):
+    """the same finite-difference checks with the lattice, the tape and the adjoint kernels on the device: a time series
+    design (OptimalControl of the inlet velocity) and a field design (InternalTopology of the reference's d2q9_adj)"""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    have = lambda n: os.path.exists(os.path.join(root, "tclb_b200", "_lib", n))
+    if not (have("libtclb_d2q9_double_ad.so") and have("libtclb_ref_d2q9_adj_double_ad.so") and have("libtclb_ref_d2q9_adj_double.so")):
+        pytest.skip("adjoint libraries were not built")
+    a, b = tmp_path / "oc", tmp_path / "topo"
+    a.mkdir(); b.mkdir()
+    (a / "ctl.csv").write_text("t,v\n" + "".join(f"{t},{0.01 + 0.004 * ((3 * t) % 5)}\n" for t in range(9)))
+    out = _run(tclb_bin, a, "d2q9", CONTROL_CASE.format(design=DESIGNS["OptimalControl"][0], fd="", tail=""), backend="gpu")
+    rows = re.findall(r"FDTest: parameter (\d+)  adjoint ([-+.eE0-9]+)  finite difference ([-+.eE0-9]+)", out)
+    assert len(rows) == 8 and any(abs(float(r[1])) > 1e-8 for r in rows)
+    for _, g, fd in rows:
+        g, fd = float(g), float(fd)
+        assert abs(g - fd) <= 1e-6 * max(abs(g), abs(fd)) + 5e-9, (g, fd)
+    out = _run(tclb_bin, b, "ref_d2q9_adj", TOPOLOGY_CASE.format(design="<InternalTopology/>", tail=""), backend="gpu")
+    assert "from 80" in out
+    worst = float(re.search(r"FDTest: largest relative difference ([-+.eE0-9]+)", out).group(1))
+    assert worst < 1e-5, out[-3000:]

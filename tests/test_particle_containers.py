@@ -99,3 +99,14 @@ def test_grid_container_gpu_matches_cpu_and_is_faster_than_the_scan(tclb_bin, tm
         t[container] = time.time() - t0
     print("10^4 particles, 128^3, 60 iterations: grid %.2f s, tree %.2f s, all %.2f s" % (t["grid"], t["tree"], t["all"]))
     assert t["all"] > 3 * t["grid"] and t["all"] > 2 * t["tree"], t
+    # the same without process start-up and initialisation: a run four times as long, rate from the difference
+    big4 = big.replace('<Solve Iterations="60"/>', '<Solve Iterations="240"/>')
+    assert big4 != big
+    rate = {}
+    for container in ("grid", "tree", "all"):
+        t0 = time.time()
+        _run(tclb_bin, tmp_path / f"big4_{container}", "gpu", container, big4)
+        rate[container] = 180.0 / max(time.time() - t0 - t[container], 1e-3)
+    print("10^4 particles, 128^3: iterations per second  grid %.0f, tree %.0f, all %.0f  (grid/all = %.1fx, tree/all = %.1fx)"
+          % (rate["grid"], rate["tree"], rate["all"], rate["grid"] / rate["all"], rate["tree"] / rate["all"]))
+    assert rate["grid"] > 5 * rate["all"], rate
