@@ -102,8 +102,9 @@ def _lattice_tables(code: str) -> str:
         if re.search(r"(?<![\w.])" + name + r"\s*\[", code) is None:
             continue
         vals = ", ".join(repr(float(x)) for x in v)
-        out.append(f"#ifdef __CUDACC__\nstatic __constant__ real_t {name}_dev_[{len(v)}] = {{{vals}}};\n#endif\n"
-                   f"static const real_t {name}_host_[{len(v)}] = {{{vals}}};\n"
+        # base_t, not real_t: constants carry no tangents, and a __constant__ array of dual numbers cannot be initialised
+        out.append(f"#ifdef __CUDACC__\nstatic __constant__ base_t {name}_dev_[{len(v)}] = {{{vals}}};\n#endif\n"
+                   f"static const base_t {name}_host_[{len(v)}] = {{{vals}}};\n"
                    f"#ifdef __CUDA_ARCH__\n#define {name} {name}_dev_\n#else\n#define {name} {name}_host_\n#endif")
     return "\n".join(out)
 
@@ -326,6 +327,29 @@ def _autosym_resolve(m: ModelDef, s, fidx) -> str:
                 L.append(f"        n.{d.name} = n.load_field({fidx[d.field]}, {-d.dx}, {-d.dy}, {-d.dz});")
             L.append("    }")
     return "\n".join(L)
+
+
+def _int_assignments_for_dual(code: str) -> str:
+    """Adjoint source only.  Model code may keep a field expression in an INTEGER variable
+    (`int solidFlag[27]; solidFlag[k] = PhaseF(1,0,0)/-998;`): an implicit real -> int conversion, which the dual-number type
+    does not offer on purpose (its conversions are explicit, so that no arithmetic silently loses its tangents).  Where the
+    model itself asks for an integer the truncation is the model's meaning (and its derivative is zero), so assignments to
+    variables declared `int` get the conversion written out.  The ordinary source is left as it is."""
+    names = set()
+    for mt in re.finditer(r"\bint\s+([A-Za-z_]\w*)\s*(\[[^\]]*\])?\s*(?=[;=,)])", code):
+        names.add(mt.group(1))
+    names -= {"i", "j", "k"} & set()          # loop counters are handled like the rest: (int)tclb_value(0) is 0
+    if not names:
+        return code
+    alt = "|".join(sorted(map(re.escape, names), key=len, reverse=True))
+    pat = re.compile(r"(?<![\w.>])(" + alt + r")(\s*\[[^\]]*\])?\s*=(?!=)\s*([^;{}]+);")
+
+    def fix(mt):
+        rhs = mt.group(3).strip()
+        if re.fullmatch(r"[-+]?\d+", rhs):     # plain integer literal: nothing to convert
+            return mt.group(0)
+        return f"{mt.group(1)}{mt.group(2) or ''} = (int)tclb_value({rhs});"
+    return pat.sub(fix, code)
 
 
 def _guard_type_switches(code: str, m: ModelDef) -> str:
@@ -785,6 +809,8 @@ struct Node {
     code = re.sub(r"\bSync(?:Full)?ParticleIterator\s+(\w+)\s*\(", r"OldParticleIterator<ParticleS, Node<GMODE> > \1(*this, ", m.code)
     code = re.sub(r"(?<![<\w])(?:Tree|Full)?ParticleIterator\s+(\w+)\s*\(", r"OldParticleIterator<ParticleI, Node<GMODE> > \1(*this, ", code)
     code = _guard_type_switches(code, m)
+    if adjoint:
+        code = _int_assignments_for_dual(code)
     A(code)
     A("#else")
     A(to_single_precision(code))

@@ -49,12 +49,14 @@ def _directional_check(d, m, n, fields, tol, frames=0, seed=3):
     return grad, held
 
 
-def _terminal_check(d, m, n, tol, seed=5):
-    """cost J = <w, state after n iterations>: w is seeded into the adjoint buffers before the backward sweep"""
+def _terminal_check(d, m, n, tol, seed=5, fields=None):
+    """cost J = <w, state after n iterations>: w is seeded into the adjoint buffers before the backward sweep; `fields`
+    restricts the weights and the perturbed direction (fields that hold flags or integer offsets are not differentiable)"""
     rng = np.random.default_rng(seed)
     base = {f: d.get_field(f).astype(np.float64) for f in m.fields}
-    w = {f: rng.standard_normal(base[f].shape) for f in m.fields}
-    direction = {f: rng.standard_normal(base[f].shape) for f in m.fields}
+    sel = set(fields) if fields is not None else set(m.fields)
+    w = {f: rng.standard_normal(base[f].shape) * (1.0 if f in sel else 0.0) for f in m.fields}
+    direction = {f: rng.standard_normal(base[f].shape) * (1.0 if f in sel else 0.0) for f in m.fields}
     adj = Adjoint(d)
     adj.record(n)
     for f in m.fields:
@@ -204,3 +206,39 @@ def test_ten_thousand_iterations_inside_a_fixed_tape_budget_gpu():
     assert held <= 64 and np.isfinite(g).all() and np.abs(g).max() > 0 and adj.objective != 0.0
     assert np.array_equal(d.get_field(m.fields[1]), after)
     adj.close(); d.close()
+
+
+def _pf_velocity_domain(m, shape, nranks):
+    nx, ny, nz = shape
+    d = Domain(m, shape, "cpu", nranks=nranks)
+    fl = np.full((nz, ny, nx), m.flag("MRT"), dtype=np.uint32)
+    fl[:, 0, :] = m.flag("Wall"); fl[:, -1, :] = m.flag("Wall")
+    d.set_flags(fl)
+    for k, v in (("Density_h", 1.0), ("Density_l", 0.1), ("PhaseField_init", 1.0), ("sigma", 1e-3), ("M", 0.05), ("IntWidth", 3.0),
+                 ("Viscosity_l", 0.16), ("Viscosity_h", 0.16), ("Radius", 4.0), ("CenterX", nx / 2), ("CenterY", ny / 2), ("CenterZ", nz / 2),
+                 ("BubbleType", -1.0), ("GravitationY", -1e-5)):
+        if k in m.settings or k in m.zonesettings:
+            d.set_setting(k, v)
+    d.init()
+    return d
+
+
+@pytest.mark.parametrize("nranks", [1, 2])
+def test_pf_velocity_adjoint_against_finite_differences(built, reference_dir, nranks):
+    """the reference's d3q27_pf_velocity (4-stage iteration, two lattices, 27 stencil reads of the phase field, integer
+    temporaries in the model code) from its own files: terminal-cost adjoint against central differences on 1 and 2 subdomains"""
+    from tclb_b200.runtime import LIBDIR
+    if not (LIBDIR / "libtclb_ref_d3q27_pf_velocity_double_ad.so").exists() and not os.environ.get("TCLB_SLOW_TESTS"):
+        pytest.skip("the adjoint library of d3q27_pf_velocity is not built (12 minutes of nvcc): TCLB_SLOW_TESTS=1 builds it here")
+    build.build_from_dir(os.path.join(reference_dir, "models/multiphase/d3q27_pf_velocity"), precision="double")
+    build.build_adjoint_lib("ref_d3q27_pf_velocity", "double")
+    m = Model("ref_d3q27_pf_velocity", "double")
+    assert len(m.actions["Iteration"]) == 4
+    d = _pf_velocity_domain(m, (12, 10, 8), nranks)
+    d.iterate(2)
+    # the populations of both lattices, the phase field and the velocity; not the wall-normal offsets and boundary marks the
+    # model also keeps in fields (`nw_x`, `IsBoundary`, ...: integers in disguise, compared with == in the model code)
+    phys = [f for f in m.fields if f[0] in "gh" and f[1:].isdigit() or f in ("PhaseF", "U", "V", "W", "pnorm")]
+    assert len(phys) >= 27 + 15 + 4
+    _terminal_check(d, m, 3, 1e-7, fields=phys)
+    d.close()
