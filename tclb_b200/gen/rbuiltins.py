@@ -1,6 +1,7 @@
 """Builtin functions of the R-subset interpreter (what Dynamics.R / Dynamics.c.Rt files of the reference call)."""
 from __future__ import annotations
 
+import os
 import math
 import re
 from collections import OrderedDict
@@ -315,6 +316,43 @@ def install(I):
             return vec(lines) if lines else np.array([], dtype=object)
         return _plain_readlines(I, a, k)
     G.set("readLines", _readlines)
+
+    def _r_num(x):
+        """a number as R's write.table prints it: up to 15 significant digits, no trailing zeros"""
+        if isinstance(x, (bool, np.bool_)):
+            return "TRUE" if x else "FALSE"
+        if isinstance(x, (int, np.integer)):
+            return str(int(x))
+        if isinstance(x, (float, np.floating)):
+            if x != x:
+                return "NA"
+            t = "%.15g" % float(x)
+            return t
+        return '"%s"' % str(x).replace('"', '""')
+
+    def _write_table(I, a, k, sep=",", header_quote=True):
+        x = a[0] if a else k.get("x")
+        file = scalar(a[1]) if len(a) > 1 else scalar(k.get("file"))
+        row_names = bool(scalar(k.get("row.names", vec(True))))
+        sep = scalar(k.get("sep", vec(sep)))
+        if not isinstance(x, DataFrame):
+            x = _data_frame(I, [x], OrderedDict())
+        cols = list(x.cols.keys())
+        n = x.nrow()
+        rn = getattr(x, "rownames", None) or [str(i + 1) for i in range(n)]
+        lines = [sep.join((['""'] if row_names else []) + ['"%s"' % c for c in cols])]
+        for i in range(n):
+            cells = [_r_num(x.cols[c][i]) for c in cols]
+            lines.append(sep.join((['"%s"' % rn[i]] if row_names else []) + cells))
+        path = str(file)
+        d = os.path.dirname(path)
+        if d:
+            os.makedirs(d, exist_ok=True)
+        with open(path, "w") as f:
+            f.write("\n".join(lines) + "\n")
+        return NULL
+    G.set("write.csv", _write_table)
+    G.set("write.table", lambda I, a, k: _write_table(I, a, k, sep=" "))
     G.set("nlevels", lambda I, a, k: vec(0))
     G.set("rows", lambda I, a, k: _rows(a[0]))
     G.set(".GlobalEnv", vec("<globalenv>"))      # assign(..., envir=.GlobalEnv): assign() always writes the global scope here

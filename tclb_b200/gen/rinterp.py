@@ -821,6 +821,11 @@ class Interp:
                 vv = np.resize(v, len(r) * len(c)).reshape(len(c), len(r)).T if v.ndim < 2 else v
                 a[np.ix_(r, c)] = vv
                 return a
+            if len(idxs) == 0 or (len(idxs) == 1 and idxs[0] is MISSING):
+                # x[] <- v: every element, the shape (and names) of x stay
+                flat = a.ravel(order="F")
+                flat[:] = np.resize(v.ravel(order="F") if v.ndim > 1 else v, flat.size)
+                return flat.reshape(a.shape, order="F") if a.ndim > 1 else flat
             names = self.names_of(cur)
             if idxs[0] is not MISSING and is_str_vec(vec(idxs[0])) and not names:
                 names = []

@@ -12,7 +12,7 @@ object ``Solver`` that offers what the reference's embedded R/Python gets (src/H
     Solver.Actions.Iterate(100)           Solver.Actions.Run("InitFields")
     Solver.Info.Iteration                 Solver.Info.Model
 
-``<RunR>`` elements are handed to the same hook and fail with a clear message (no R in this framework).
+``<RunR>`` elements are handed to the same hook and run in this repository's R-subset interpreter (`Solver._run_r`).
 """
 from __future__ import annotations
 
@@ -290,11 +290,81 @@ class Solver:
         except Exception:
             pass
 
+    # ---- <RunR> ----
+    def _run_r(self, src: str, iteration: int):
+        """<RunR> without R: the block runs in this repository's R-subset interpreter (tclb_b200/gen/rinterp.py, the one that
+        executes the models' Dynamics.R) with a `Solver` list of the same shape the reference's RInside bridge offers
+        (src/Handlers/cbRunR.cpp:484-520, 751-845): Solver$Settings$<name>, Solver$Globals$<name>, Solver$Quantities$<name>,
+        Solver$Fields$<name>, Solver$Geometry$X|Y|Z, Solver$Iteration.  Lattice arrays are vectors in the lattice's memory
+        order (x fastest; a vector quantity is 3 x nodes).  Only what the block mentions is materialised; after the block,
+        fields and settings it changed are written back.  The language coverage is the interpreter's (vector arithmetic,
+        data frames, apply-family, control flow, write.csv), not all of R."""
+        import re
+
+        from .gen.rinterp import Interp
+        from .gen.rlang import RList, vec
+        m, d = self.model, self.domain
+        used = lambda kind: sorted(set(a or b for a, b in re.findall(r"Solver\$" + kind + r"\$(?:`([^`]+)`|([A-Za-z_.][\w.]*))", src)))
+        S = RList()
+        st = RList()
+        for k in list(m.settings) + list(m.zonesettings):
+            st[k] = vec(float(d.get_setting(k)))
+        S["Settings"] = st
+        gl = RList()
+        if "Solver$Globals" in src:
+            for k, v in d.globals().items():
+                gl[k] = vec(float(v))
+        S["Globals"] = gl
+        q = RList()
+        for k in used("Quantities"):
+            if k not in m.quantities:
+                raise RuntimeError(f"<RunR>: the model has no quantity {k}")
+            a = d.get_quantity(k)
+            q[k] = np.ascontiguousarray(a, dtype=np.float64).reshape(-1, 3).T.copy() if m.quantities[k] else np.asarray(a, dtype=np.float64).ravel()
+        S["Quantities"] = q
+        f = RList()
+        for k in used("Fields"):
+            if k not in m.fields:
+                raise RuntimeError(f"<RunR>: the model has no field {k}")
+            f[k] = np.asarray(d.get_field(k), dtype=np.float64).ravel()
+        S["Fields"] = f
+        g = RList()
+        geo = _Geometry(self)
+        for k in used("Geometry"):
+            if k in ("X", "Y", "Z"):
+                g[k] = np.asarray(getattr(geo, k), dtype=np.float64).ravel()
+            else:
+                raise RuntimeError(f"<RunR>: Solver$Geometry${k} is not available here (X, Y, Z are)")
+        S["Geometry"] = g
+        S["Iteration"] = vec(float(iteration))
+        before_fields = {k: np.array(v, copy=True) for k, v in f.items()}
+        before_settings = {k: float(np.asarray(v).ravel()[0]) for k, v in st.items()}
+        I = getattr(self, "_r_interp", None)
+        if I is None:
+            I = self._r_interp = Interp()
+        I.globals.set("Solver", S)
+        I.run(src, I.globals)
+        S2 = I.globals.get("Solver")
+        nx, ny, nz = d.shape
+        for k, v in S2["Fields"].items():
+            a = np.asarray(v, dtype=np.float64).ravel()
+            if k not in m.fields:
+                raise RuntimeError(f"<RunR>: the model has no field {k}")
+            if k not in before_fields or a.shape != before_fields[k].shape or not np.array_equal(a, before_fields[k]):
+                d.set_field(k, np.resize(a, nx * ny * nz).reshape(nz, ny, nx))
+        for k, v in S2["Settings"].items():
+            x = float(np.asarray(v).ravel()[0])
+            if k not in before_settings:
+                raise RuntimeError(f"<RunR>: the model has no setting {k}")
+            if x != before_settings[k]:
+                d.set_setting(k, x)
+
     # ---- <RunPython> ----
     def _on_script(self, user, element, code, iteration) -> int:
         try:
             if element.decode() == "RunR":
-                raise RuntimeError("<RunR> needs an R interpreter; rewrite the block as <RunPython> (same Solver object)")
+                self._run_r(_dedent(code.decode()), iteration)
+                return 0
             src = _dedent(code.decode())
             ns = self.namespace
             ns.setdefault("np", np)

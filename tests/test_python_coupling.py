@@ -60,3 +60,54 @@ def test_runpython_without_python_host_fails_cleanly(tclb_bin, tmp_path):
     (tmp_path / "c.xml").write_text(CASE)
     r = subprocess.run([tclb_bin, "--cpu", "d2q9", "c.xml"], cwd=tmp_path, capture_output=True, text=True)
     assert r.returncode != 0 and "tclb_b200.run" in (r.stdout + r.stderr)
+
+
+R_CASE = """<?xml version="1.0"?>
+<CLBConfig version="2.0" output="output/">
+  <Geometry nx="32" ny="16">
+    <MRT><Box/></MRT>
+    <Wall mask="ALL"><Channel/></Wall>
+  </Geometry>
+  <Model>
+    <Param name="Viscosity" value="0.05"/>
+  </Model>
+  <RunR>
+    x = (Solver$Geometry$X - 0.5) / 32
+    y = (Solver$Geometry$Y - 0.5) / 16
+    Solver$Fields$rho_field_probe = 0                  # no such field: ignored unless written back, see the test below
+  </RunR>
+  <Solve Iterations="10"/>
+  <RunR>
+    nu0 = Solver$Settings$Viscosity
+    Solver$Settings$Viscosity = nu0 * 2
+    f3 = Solver$Fields$f3
+    x = (Solver$Geometry$X - 0.5) / 32
+    Solver$Fields$f3[] = 0.1 + 0.01 * sin(2 * pi * x)
+    u = Solver$Quantities$U
+    write.csv(data.frame(it = Solver$Iteration, umax = max(abs(u)), n = length(f3)), "output/r_probe.csv", row.names = FALSE)
+  </RunR>
+</CLBConfig>
+"""
+
+
+def test_runr_blocks_run_in_the_r_subset_interpreter(built, tmp_path, monkeypatch):
+    """<RunR> (reference src/Handlers/cbRunR.cpp) without R: settings, fields, quantities, geometry coordinates through
+    a `Solver` list; what the block changes is written back to the lattice"""
+    from tclb_b200 import build
+    from tclb_b200.solver import Solver
+    build.build_model_lib("d2q9", "double")
+    monkeypatch.chdir(tmp_path)
+    s = Solver("d2q9", "double", "cpu")
+    case = R_CASE.replace("    Solver$Fields$rho_field_probe = 0                  # no such field: ignored unless written back, see the test below\n", "")
+    fname = s.model.fields[3]
+    case = case.replace("Solver$Fields$f3", "Solver$Fields$`%s`" % fname if not fname.isidentifier() else "Solver$Fields$" + fname)
+    s.load_string(case, "rcase").run()
+    assert abs(s.domain.get_setting("Viscosity") - 0.1) < 1e-15
+    f3 = s.domain.get_field(fname)
+    x = (np.arange(32) + 0.5 - 0.5) / 32
+    assert np.allclose(f3[0], 0.1 + 0.01 * np.sin(2 * np.pi * x)[None, :], rtol=0, atol=1e-15)
+    rows = open(tmp_path / "output" / "r_probe.csv").read().split("\n")
+    assert rows[0] == '"it","umax","n"'
+    it, umax, n = rows[1].split(",")
+    assert float(it) == 10 and float(umax) >= 0 and int(float(n)) == 32 * 16
+    s.close()
