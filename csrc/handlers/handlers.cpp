@@ -926,6 +926,21 @@ class AcRemoteForceInterface : public Action {
 };
 TCLB_REGISTER_HANDLER("RemoteForceInterface", AcRemoteForceInterface)
 
+// <ESYSParticle>: the reference writes a driver script for ESyS-Particle and starts it with MPI_Comm_spawn
+// (src/Handlers/acESYSParticle.cpp:6-260).  Neither ESyS-Particle nor MPI exists here; an ESyS driver that speaks the bridge
+// protocol (csrc/host/rfi_bridge.h) is started like any external integrator, so the element says how instead of failing mutely.
+class AcESYSParticle : public Action {
+  public:
+    int init() override {
+        Action::init();
+        logf(L_ERROR, "<ESYSParticle>: ESyS-Particle is not part of this installation. Couple an external integrator with "
+                      "<RemoteForceInterface integrator=\"ESYSPARTICLE\" spawn=\"program args\"/> (or connect=\"socket\"); "
+                      "the program serves tclb::rfi_serve() or speaks the protocol documented in csrc/host/rfi_bridge.h");
+        return -1;
+    }
+};
+TCLB_REGISTER_HANDLER("ESYSParticle", AcESYSParticle)
+
 // <RunPython> / <RunR> (reference src/Handlers/cbRunR.cpp): the code runs inside the embedding Python process through
 // the script hook (tclb_solver_set_script_hook; tclb_b200.runtime.Solver installs one that exposes the same object
 // surface: Solver.Settings/Fields/Quantities/Globals/Geometry/Actions/Info).  Without a hook (plain bin/tclb) the
