@@ -873,7 +873,10 @@ class AcRemoteForceInterface : public Action {
         Action::init();
         std::string name = node->attr("integrator");
         if (name.empty()) { logf(L_ERROR, "You must specify RemoteForceInterface integrator name"); return -1; }
-        if (node->has_attr("spawn") || node->has_attr("connect")) {
+        // TCLB_RFI_CONNECT=/path/to/socket: the launcher started the integrator program next to this one (the reference's
+        // `mpirun main case.xml : simplepart part.xml`), the case file itself names no socket
+        const char *env_connect = getenv("TCLB_RFI_CONNECT");
+        if (node->has_attr("spawn") || node->has_attr("connect") || (env_connect && *env_connect)) {
             std::unique_ptr<RemoteIntegrator> ri(new RemoteIntegrator());
             const int workers = (int)solver->domain->local.size();
             bool ok;
@@ -881,8 +884,9 @@ class AcRemoteForceInterface : public Action {
                 logf(L_OUTPUT, "Connecting RFI to %s (starting: %s)", name.c_str(), node->attr("spawn").c_str());
                 ok = ri->spawn(node->attr("spawn"), workers, node->attr_bool("omega"), node->attr_bool("torque"));
             } else {
-                logf(L_OUTPUT, "Connecting RFI to %s (socket %s)", name.c_str(), node->attr("connect").c_str());
-                ok = ri->connect_to(node->attr("connect"), workers, node->attr_bool("omega"), node->attr_bool("torque"));
+                const std::string sock = node->has_attr("connect") ? node->attr("connect") : std::string(env_connect);
+                logf(L_OUTPUT, "Connecting RFI to %s (socket %s)", name.c_str(), sock.c_str());
+                ok = ri->connect_to(sock, workers, node->attr_bool("omega"), node->attr_bool("torque"));
             }
             if (!ok) { logf(L_ERROR, "RemoteForceInterface: %s", ri->error.c_str()); return -1; }
             solver->integrator.reset(ri.release());

@@ -93,3 +93,7 @@ def test_reference_particle_suite_passes(reference_dir, tclb_bin):
     r = subprocess.run(["python", os.path.join(root, "tools", "run_tests.py"), "d3q27_PSM_NEBB", os.path.join(reference_dir, "tests/external/d3q27_PSM_NEBB"),
                         "--library", "ref_d3q27_PSM_NEBB"], capture_output=True, text=True, timeout=1800)
     assert r.returncode == 0 and "3 of 3 tests passed" in r.stdout, r.stdout[-3000:]
+    # the same suite with the launch lines taken literally: solver and `simplepart` as two programs (socket bridge)
+    r = subprocess.run(["python", os.path.join(root, "tools", "run_tests.py"), "d3q27_PSM_NEBB", os.path.join(reference_dir, "tests/external/d3q27_PSM_NEBB"),
+                        "--library", "ref_d3q27_PSM_NEBB", "--mpmd"], capture_output=True, text=True, timeout=1800)
+    assert r.returncode == 0 and "3 of 3 tests passed" in r.stdout, r.stdout[-3000:]

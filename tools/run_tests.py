@@ -24,7 +24,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 VTI_EPS_FLOOR = float(os.environ.get("TCLB_VTI_EPS_FLOOR", "1e6"))
 
 
-def run_one(test_file, model, lib, flags, verbose):
+def run_one(test_file, model, lib, flags, verbose, mpmd=False):
     tdir = os.path.dirname(os.path.abspath(test_file))
     wd = tempfile.mkdtemp(prefix="tclb_test_")
     ok = True
@@ -54,10 +54,24 @@ def run_one(test_file, model, lib, flags, verbose):
                     continue
                 else:
                     rest.append(a)
+            env, integ = None, None
             if len(side) > 1 and side[0].endswith("simplepart"):
-                opts += ["--simplepart", side[1]]
+                if mpmd:
+                    # two programs, like the reference's MPMD launch: the integrator listens, the solver connects
+                    sock = os.path.join(wd, "rfi.sock")
+                    integ = subprocess.Popen([os.path.join(ROOT, "bin", "tclb-integrator"), "simplepart", side[1], "--listen", sock] +
+                                             (["--omega"] if "omega" in open(os.path.join(wd, rest[0])).read() else []), cwd=wd,
+                                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+                    env = dict(os.environ, TCLB_RFI_CONNECT=sock)
+                else:
+                    opts += ["--simplepart", side[1]]
             argv = [os.path.join(ROOT, "bin", "tclb")] + flags + opts + [lib] + rest
-            r = subprocess.run(argv, cwd=wd, capture_output=True, text=True)
+            r = subprocess.run(argv, cwd=wd, capture_output=True, text=True, env=env)
+            if integ is not None:
+                try:
+                    integ.communicate(timeout=60)
+                except subprocess.TimeoutExpired:
+                    integ.kill()
             good = (r.returncode == 0) if cmd == "run" else (r.returncode != 0)
             if not good:
                 print(f"  {cmd} FAILED: {' '.join(argv)}\n{r.stdout[-1500:]}{r.stderr[-1500:]}")
@@ -126,12 +140,13 @@ def main():
     ap.add_argument("--gpu", action="store_true")
     ap.add_argument("--precision", default="double")
     ap.add_argument("-v", "--verbose", action="store_true")
+    ap.add_argument("--mpmd", action="store_true", help="side programs of a test (simplepart) run as separate programs coupled over the RFI socket bridge instead of in-process")
     a = ap.parse_args()
     tests = [os.path.join(a.directory, t) for t in a.tests] if a.tests else sorted(glob.glob(os.path.join(a.directory, "*.test")))
     flags = ["--gpu" if a.gpu else "--cpu", "--precision", a.precision]
     bad = 0
     for t in tests:
-        ok = run_one(t, a.model, a.library or a.model, flags, a.verbose)
+        ok = run_one(t, a.model, a.library or a.model, flags, a.verbose, a.mpmd)
         print(f"{'OK  ' if ok else 'FAIL'} {os.path.basename(t)}")
         bad += 0 if ok else 1
     print(f"{len(tests) - bad} of {len(tests)} tests passed")
