@@ -31,7 +31,7 @@ ELEMENTS = {
     "Container": ("container", "", "grouping"),
     "EvalIf": ("container", "opt_present opt_missing", "children run only if the model has / lacks an option"),
     "VTK": ("callback", "Iterations name what dx dy dz nx ny nz", "ImageData pieces + .pvti index"),
-    "HDF5": ("callback", "Iterations name what compress write_xdmf point_data precision dx dy dz nx ny nz", "one .h5 for the output region + .xmf (3DCoRectMesh) index"),
+    "HDF5": ("callback", "Iterations name what compress write_xdmf point_data precision dx dy dz nx ny nz", "one .h5 for the output region + .xmf (3DCoRectMesh) index; one process per GPU: one piece per rank + an XDMF spatial collection"),
     "TXT": ("callback", "Iterations name what gzip", "one text file per quantity"),
     "BIN": ("callback", "Iterations name", "raw binary per quantity"),
     "Log": ("callback", "Iterations name", "CSV log of settings, zone settings and Globals"),
@@ -50,15 +50,26 @@ ELEMENTS = {
     "Control": ("action", "Iterations", "time-dependent zonal settings from <CSV file Time> + <Param value=expr>"),
     "SyntheticTurbulence": ("action", "Modes Spread Spectrum *WaveLength *WaveNumber *WaveFrequency", "random Fourier modes for turbulent inlets"),
     "RunPython": ("callback", "Iterations file", "Python code with the Solver object (python -m tclb_b200.run)"),
-    "Adjoint": ("container", "type Iterations", "type=unsteady: children run with every iteration on the tape, then the reverse sweep; type=steady: Iterations adjoint iterations around the state the children left"),
-    "Objective": ("action", "<Global>=weight ...", "weights of SUM Globals in the objective (sets the <Global>InObj zonal settings)"),
-    "FDTest": ("container", "Samples Epsilon", "adjoint gradient against central differences for a few design variables (children re-run from the same state)"),
+    "Adjoint": ("container", "type Iterations tape", "type=unsteady: children run with every iteration on the tape, then the reverse sweep; type=steady: Iterations adjoint iterations around the state the children left"),
+    "Objective": ("action", "<objective>=weight ...", "weighted model objectives (every Global, and AddObjective expressions of the Globals) linearised at the current Globals into the <Global>InObj zonal settings"),
+    "FDTest": ("container", "Samples Epsilon parameters", "adjoint gradient against central differences for some (parameters=\"a:b\") or all design parameters (children re-run from the same state)"),
     "OptSolve": ("action", "Iterations Descent direction", "one-shot optimisation: primal iteration + adjoint iteration + descent step of the parameter fields"),
-    "Optimize": ("container", "MaxEvaluations method Step", "maximises the objective accumulated by the children over the parameter fields (built-in projected gradient method)"),
+    "Optimize": ("container", "MaxEvaluations method Material XAbsTolerance RelTolerance AbsTolerance StopAtValue Step", "maximises the objective accumulated by the children over the design parameters; method = MMA, LBFGS, NELDERMEAD (= COBYLA), GD (built in)"),
+    "OptimalControl": ("design", "what lower upper", "time series of a zonal setting (what=\"Setting-Zone\") as design parameters"),
+    "OptimalControlSecond": ("design", "what lower upper", "every second time level of a zonal setting, the levels in between interpolated"),
+    "Fourier": ("design", "modes lower upper", "wraps one design child: its parameters as a truncated Fourier series"),
+    "BSpline": ("design", "nodes order periodic lower upper", "wraps one design child: its parameters as a B-spline"),
+    "RepeatControl": ("design", "length flip lower upper", "wraps one design child: a pattern of `length` parameters repeated (optionally mirrored)"),
+    "InternalTopology": ("design", "", "the parameter fields on the DesignSpace nodes as design parameters"),
+    "FieldParameter": ("design", "field where zone", "one field on the nodes of a node type / zone as design parameters"),
+    "ControlParameter": ("design", "", "parameters of a <Control> element as design parameters"),
+    "Extrude": ("design", "direction theta margin", "wraps one design child: parameters constant along one direction (x, y, z or t)"),
     "Threshold": ("container", "Levels", "runs the children on thresholded copies of the design, level i/Levels"),
     "ThresholdNow": ("action", "Level", "thresholds the parameter fields to 0/1"),
     "Andersen": ("container", "Directions Times Eps", "Anderson mixing of the fixed-point iteration state -> children(state)"),
-    "RunR": ("callback", "Iterations file", "recognised; R is not available, rewrite as RunPython"),
+    "RunR": ("callback", "Iterations file", "R code with the Solver list, run in the R-subset interpreter (python -m tclb_b200.run)"),
+    "RemoteForceInterface": ("action", "integrator omega torque spawn connect", "particle coupling: built-in SIMPLEPART (child <SimplePart>), or an external integrator program started (spawn=) or listening (connect=)"),
+    "ESYSParticle": ("action", "", "recognised; points to RemoteForceInterface spawn=/connect= (ESyS-Particle is not installed)"),
     "Catalyst": ("callback", "", "recognised; unavailable on this box"),
     "Run": ("marker", "", "ignored"),
 }
