@@ -481,6 +481,7 @@ typedef base_t storage_t;
     A("#ifndef TCLB_ELECT\n#define TCLB_ELECT %d\n#endif" % int(tun.get("elect", 0)))
     A("// true inside the node code of the persistent kernels (compile-time constant of the Node<GMODE> instance)")
     A("#define TCLB_NODE_PERSISTENT ((GMODE & 8) != 0)")
+    A("#ifndef TCLB_FUSED_PUBLISH\n#define TCLB_FUSED_PUBLISH %d\n#endif" % int(tun.get("fused_publish", 1)))
     A("#define TCLB_PLAIN_MASK %du" % plain_mask)
     A("#ifndef TCLB_FASTPATH\n#define TCLB_FASTPATH %d\n#endif" % int(tun.get("fastpath", 0)))
     A("#ifndef TCLB_PERSIST_MIN_BLOCKS\n#ifdef TCLB_DOUBLE\n#define TCLB_PERSIST_MIN_BLOCKS %d\n#else\n#define TCLB_PERSIST_MIN_BLOCKS %d\n#endif\n#endif"
@@ -1213,6 +1214,7 @@ const tclb_model_t t_model = {{
 }};
 }}  // namespace
 extern "C" const tclb_model_t *tclb_get_model(void) {{ return &t_model; }}
+extern "C" long long tclb_model_launch_count(void) {{ return g_launch_count; }}
 #endif  // !TCLB_AD
 """)
     return "\n".join(L) + "\n"
