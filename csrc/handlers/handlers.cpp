@@ -371,6 +371,14 @@ class AcSyntheticTurbulence : public Action {
             m.a[2] = t[0] * t[4] - t[1] * t[3];
             m.freq = 0;      // the reference stores TimeWN but its device evaluation does not use it
         }
+        if (timeWN != 0) {
+            // the time wave number travels as the frequency of one more mode of zero amplitude (it adds exactly nothing to the
+            // velocity): node code that asks for `constContainer.ST.TimeWN` (models/heat/experimental/d3q27_cumulant_heat) reads it there
+            tclb_st_mode_t m;
+            for (int i = 0; i < 3; i++) { m.k[i] = 0; m.a[i] = 0; m.b[i] = 0; }
+            m.freq = timeWN;
+            modes.push_back(m);
+        }
         for (int r : solver->domain->local) solver->domain->lat[r]->set_synthetic_turbulence(modes);
         return 0;
     }

@@ -329,6 +329,22 @@ def _autosym_resolve(m: ModelDef, s, fidx) -> str:
     return "\n".join(L)
 
 
+# node code of a few older models reads the synthetic-turbulence time wave number straight from the reference's constant
+# container (`constContainer.ST.TimeWN`, models/heat/experimental/d3q27_cumulant_heat); the value travels as the frequency of
+# a trailing zero-amplitude mode (csrc/handlers/handlers.cpp, AcSyntheticTurbulence)
+_CONST_CONTAINER = """    struct ConstContainerST_ { real_t TimeWN; };
+    struct ConstContainer_ { ConstContainerST_ ST; };
+    TCLB_HD ConstContainer_ const_container_() const {
+        ConstContainer_ c;
+        c.ST.TimeWN = ka_.st_n > 0 ? (real_t)ka_.st[ka_.st_n - 1].freq : (real_t)0;
+        return c;
+    }
+#define constContainer const_container_()
+    // the one-argument call of the same generation of model files: the field at this node
+    TCLB_HD vector_t SyntheticTurbulence(real_t) const { return SyntheticTurbulence(X, Y, Z); }
+"""
+
+
 def _int_assignments_for_dual(code: str) -> str:
     """Adjoint source only.  Model code may keep a field expression in an INTEGER variable
     (`int solidFlag[27]; solidFlag[k] = PhaseF(1,0,0)/-998;`): an implicit real -> int conversion, which the dual-number type
@@ -777,7 +793,7 @@ struct Node {
     TCLB_HD uint16_t getQ(int d) const {
         return ka_.cuts ? ka_.cuts[(long long)d * ((long long)ka_.nx * ka_.NY * ka_.NZ) + n_idx] : (uint16_t)NO_CUT;
     }
-    TCLB_HD vector_t SyntheticTurbulence(real_t x, real_t y, real_t z) const {
+@CONST_CONTAINER@    TCLB_HD vector_t SyntheticTurbulence(real_t x, real_t y, real_t z) const {
         vector_t v; v.x = 0; v.y = 0; v.z = 0;
         for (int i = 0; i < ka_.st_n; i++) {
             const tclb_st_mode_t &w = ka_.st[i];
@@ -804,7 +820,7 @@ struct Node {
     }
 // ---------------------------------------------------------------- model physics ----
 #ifdef TCLB_DOUBLE
-""")
+""".replace("@CONST_CONTAINER@", _CONST_CONTAINER if "constContainer" in m.code else ""))
     # older iterator form of some shipped models: `for (ParticleIterator p(X,Y,Z); p; ++p)` declares the iterator as an object
     # (also the Tree.../Full... spellings of earlier container generations)
     code = re.sub(r"\bSync(?:Full)?ParticleIterator\s+(\w+)\s*\(", r"OldParticleIterator<ParticleS, Node<GMODE> > \1(*this, ", m.code)
