@@ -97,3 +97,29 @@ def test_reference_particle_suite_passes(reference_dir, tclb_bin):
     r = subprocess.run(["python", os.path.join(root, "tools", "run_tests.py"), "d3q27_PSM_NEBB", os.path.join(reference_dir, "tests/external/d3q27_PSM_NEBB"),
                         "--library", "ref_d3q27_PSM_NEBB", "--mpmd"], capture_output=True, text=True, timeout=1800)
     assert r.returncode == 0 and "3 of 3 tests passed" in r.stdout, r.stdout[-3000:]
+
+
+def test_older_model_idioms_build_and_run(reference_dir, built):
+    """model files written against earlier generations of the reference's node interface: the synthetic-turbulence time wave
+    number read from `constContainer.ST.TimeWN` and the one-argument `SyntheticTurbulence(0)` (heat/experimental/
+    d3q27_cumulant_heat), `for (ParticleIterator p(X,Y,Z); p; ++p)` (flow/d2q9_par)"""
+    import numpy as np
+    from tclb_b200 import build
+    from tclb_b200.runtime import Domain, Model
+    build.build_from_dir(os.path.join(reference_dir, "models/heat/experimental/d3q27_cumulant_heat"), precision="double")
+    m = Model("ref_d3q27_cumulant_heat", "double")
+    assert "WVelocityTurbulent" in m.nodetypes and "T" in m.quantities
+    d = Domain(m, (16, 12, 8), "cpu")
+    fl = np.full((8, 12, 16), m.flag("MRT"), dtype=np.uint32)
+    fl[:, 0, :] = m.flag("Wall"); fl[:, -1, :] = m.flag("Wall")
+    fl[:, 1:-1, 0] = m.flag("MRT", "WVelocityTurbulent")
+    d.set_flags(fl)
+    for k, v in (("nu", 0.05), ("ForceX", 1e-5), ("Velocity", 0.01)):
+        if k in m.settings or k in m.zonesettings:
+            d.set_setting(k, v)
+    d.init(); d.iterate(20)
+    u = d.get_quantity("U")
+    assert np.isfinite(u).all() and np.abs(u).max() > 0
+    d.close()
+    src = build.build_from_dir(os.path.join(reference_dir, "models/flow/d2q9_par"), precision="double")
+    assert os.path.exists(str(src))
