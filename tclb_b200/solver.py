@@ -295,9 +295,9 @@ class Solver:
         """<RunR> without R: the block runs in this repository's R-subset interpreter (tclb_b200/gen/rinterp.py, the one that
         executes the models' Dynamics.R) with a `Solver` list of the same shape the reference's RInside bridge offers
         (src/Handlers/cbRunR.cpp:484-520, 751-845): Solver$Settings$<name>, Solver$Globals$<name>, Solver$Quantities$<name>,
-        Solver$Fields$<name>, Solver$Geometry$X|Y|Z, Solver$Iteration.  Lattice arrays are vectors in the lattice's memory
+        Solver$Fields$<name>, Solver$Geometry$X|Y|Z, Solver$Geometry$<GROUP> (node-type names per node), Solver$Iteration.  Lattice arrays are vectors in the lattice's memory
         order (x fastest; a vector quantity is 3 x nodes).  Only what the block mentions is materialised; after the block,
-        fields and settings it changed are written back.  The language coverage is the interpreter's (vector arithmetic,
+        fields, settings and node types it changed are written back.  The language coverage is the interpreter's (vector arithmetic,
         data frames, apply-family, control flow, write.csv), not all of R."""
         import re
 
@@ -333,10 +333,13 @@ class Solver:
         for k in used("Geometry"):
             if k in ("X", "Y", "Z"):
                 g[k] = np.asarray(getattr(geo, k), dtype=np.float64).ravel()
+            elif k in m.nodegroups and k != "SETTINGZONE":
+                g[k] = np.array([str(x) for x in _GroupView(geo, k).names().ravel()], dtype=object)    # node-type names per node
             else:
-                raise RuntimeError(f"<RunR>: Solver$Geometry${k} is not available here (X, Y, Z are)")
+                raise RuntimeError(f"<RunR>: Solver$Geometry${k} is not available here (X, Y, Z and the node-type groups are)")
         S["Geometry"] = g
         S["Iteration"] = vec(float(iteration))
+        before_groups = {k: np.array(v, copy=True) for k, v in g.items() if k not in ("X", "Y", "Z")}
         before_fields = {k: np.array(v, copy=True) for k, v in f.items()}
         before_settings = {k: float(np.asarray(v).ravel()[0]) for k, v in st.items()}
         I = getattr(self, "_r_interp", None)
@@ -352,6 +355,22 @@ class Solver:
                 raise RuntimeError(f"<RunR>: the model has no field {k}")
             if k not in before_fields or a.shape != before_fields[k].shape or not np.array_equal(a, before_fields[k]):
                 d.set_field(k, np.resize(a, nx * ny * nz).reshape(nz, ny, nx))
+        for k, old_names in before_groups.items():
+            now = np.array([str(x) for x in np.asarray(S2["Geometry"][k], dtype=object).ravel()], dtype=object)
+            if now.shape != old_names.shape:
+                raise RuntimeError(f"<RunR>: Solver$Geometry${k} changed its length")
+            changed = now != old_names
+            if changed.any():
+                fl = geo.flags()
+                flat = fl.reshape(-1)
+                mask = np.uint32(m.nodegroups[k][0])
+                for name in sorted(set(now[changed].tolist())):
+                    if name not in ("None", "") and (name not in m.nodetypes or m.nodetypes[name][1] != int(mask)):
+                        raise RuntimeError(f"<RunR>: {name} is not a node type of group {k}")
+                    val = np.uint32(0 if name in ("None", "") else m.nodetypes[name][0])
+                    sel = changed & (now == name)
+                    flat[sel] = (flat[sel] & ~mask) | val
+                d.set_flags(fl)
         for k, v in S2["Settings"].items():
             x = float(np.asarray(v).ravel()[0])
             if k not in before_settings:

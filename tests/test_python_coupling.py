@@ -71,11 +71,13 @@ R_CASE = """<?xml version="1.0"?>
   <Model>
     <Param name="Viscosity" value="0.05"/>
   </Model>
-  <RunR>
+  <RunR><![CDATA[
     x = (Solver$Geometry$X - 0.5) / 32
     y = (Solver$Geometry$Y - 0.5) / 16
-    Solver$Fields$rho_field_probe = 0                  # no such field: ignored unless written back, see the test below
-  </RunR>
+    sel = (x > 0.4) & (x < 0.6) & (y < 0.5)
+    Solver$Geometry$BOUNDARY[sel] = "Wall"
+    Solver$Geometry$COLLISION[sel] = "None"
+  ]]></RunR>
   <Solve Iterations="10"/>
   <RunR>
     nu0 = Solver$Settings$Viscosity
@@ -98,11 +100,17 @@ def test_runr_blocks_run_in_the_r_subset_interpreter(built, tmp_path, monkeypatc
     build.build_model_lib("d2q9", "double")
     monkeypatch.chdir(tmp_path)
     s = Solver("d2q9", "double", "cpu")
-    case = R_CASE.replace("    Solver$Fields$rho_field_probe = 0                  # no such field: ignored unless written back, see the test below\n", "")
+    case = R_CASE
     fname = s.model.fields[3]
     case = case.replace("Solver$Fields$f3", "Solver$Fields$`%s`" % fname if not fname.isidentifier() else "Solver$Fields$" + fname)
     s.load_string(case, "rcase").run()
     assert abs(s.domain.get_setting("Viscosity") - 0.1) < 1e-15
+    fl = s.domain.get_flags()
+    wall = (fl & s.model.nodetypes["Wall"][1]) == s.model.nodetypes["Wall"][0]
+    xs, ys = (np.arange(32) + 0.0) / 32, (np.arange(16) + 0.0) / 16
+    painted = ((xs > 0.4) & (xs < 0.6))[None, :] & (ys < 0.5)[:, None]
+    assert wall[0][painted].all() and not wall[0][1:-1][:, :8].any()              # the block painted by the R code, nothing else inside
+    assert ((fl[0][painted] & s.model.nodegroups["COLLISION"][0]) == 0).all()
     f3 = s.domain.get_field(fname)
     x = (np.arange(32) + 0.5 - 0.5) / 32
     assert np.allclose(f3[0], 0.1 + 0.01 * np.sin(2 * np.pi * x)[None, :], rtol=0, atol=1e-15)
