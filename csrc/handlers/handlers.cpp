@@ -573,6 +573,58 @@ class CbBIN : public Callback {
 };
 TCLB_REGISTER_HANDLER("BIN", CbBIN)
 
+// <Image Iterations=N [name="Image"] [plane=z] [scale=s]>: the picture the reference's interactive window shows
+// (velocity magnitude through its colour map, walls grey: src/LatticeContainer.inc.cpp.Rt:355-423, drawn into an OpenGL
+// pixel buffer by src/gpu_anim.h) written as a binary PPM per call; there is no window system here, the colour kernel is
+// the same headless.  One file for the whole lattice when every subdomain is in this process, else one piece per rank.
+class CbImage : public Callback {
+    std::string nm;
+    int plane = 0;
+    float scale = 1.0f;
+  public:
+    int init() override {
+        Callback::init();
+        nm = node->attr("name", "Image");
+        plane = node->has_attr("plane") ? atoi(node->attr("plane").c_str()) : solver->domain->dec.tot[2] / 2;
+        scale = node->has_attr("scale") ? (float)atof(node->attr("scale").c_str()) : 1.0f;
+        return 0;
+    }
+    static int write_ppm(const std::string &file, int w, int h, const std::vector<unsigned char> &rgba) {
+        make_parent_dirs(file);
+        FILE *f = fopen(file.c_str(), "wb");
+        if (!f) { logf(L_ERROR, "cannot write %s", file.c_str()); return -1; }
+        fprintf(f, "P6\n%d %d\n255\n", w, h);
+        std::vector<unsigned char> row((size_t)w * 3);
+        for (int y = h - 1; y >= 0; y--) {                 // image rows from the top: y grows upwards in the lattice
+            for (int x = 0; x < w; x++) for (int c = 0; c < 3; c++) row[(size_t)x * 3 + c] = rgba[((size_t)y * w + x) * 4 + c];
+            fwrite(row.data(), 1, row.size(), f);
+        }
+        fclose(f);
+        return 0;
+    }
+    int do_it() override {
+        Domain *D = solver->domain.get();
+        bool all_local = true;
+        for (int r = 0; r < D->dec.nranks; r++) if (!D->lat[r]) all_local = false;
+        const int W = D->dec.tot[0], H = D->dec.tot[1];
+        std::vector<unsigned char> whole(all_local ? (size_t)W * H * 4 : 0, 0);
+        for (int r : D->local) {
+            Lattice *l = D->lat[r];
+            const Box &b = D->dec.boxes[r];
+            if (plane < b.z0 || plane >= b.z0 + b.nz) continue;
+            std::vector<unsigned char> piece((size_t)l->nx * l->ny * 4);
+            l->color(plane - b.z0, scale, piece.data());
+            if (all_local) {
+                for (int y = 0; y < l->ny; y++)
+                    memcpy(&whole[((size_t)(y + b.y0) * W + b.x0) * 4], &piece[(size_t)y * l->nx * 4], (size_t)l->nx * 4);
+            } else if (write_ppm(solver->out_iter_file(nm, ".ppm", r), l->nx, l->ny, piece)) return -1;
+        }
+        if (all_local) return write_ppm(solver->out_iter_collective_file(nm, ".ppm"), W, H, whole);
+        return 0;
+    }
+};
+TCLB_REGISTER_HANDLER("Image", CbImage)
+
 class CbLog : public Callback {                      // reference cbLog.cpp:5-29
     std::string filename;
     int old_type = 0;

@@ -33,6 +33,7 @@ ELEMENTS = {
     "VTK": ("callback", "Iterations name what dx dy dz nx ny nz", "ImageData pieces + .pvti index"),
     "HDF5": ("callback", "Iterations name what compress write_xdmf point_data precision dx dy dz nx ny nz", "one .h5 for the output region + .xmf (3DCoRectMesh) index; one process per GPU: one piece per rank + an XDMF spatial collection"),
     "TXT": ("callback", "Iterations name what gzip", "one text file per quantity"),
+    "Image": ("callback", "Iterations name plane scale", "the picture of the reference's interactive view (colour kernel of one z-plane) as a binary PPM"),
     "BIN": ("callback", "Iterations name", "raw binary per quantity"),
     "Log": ("callback", "Iterations name", "CSV log of settings, zone settings and Globals"),
     "Stop": ("callback", "Iterations Times *Change *PercentChange *Above *Below", "stops the loop on a Global criterion"),

@@ -98,3 +98,21 @@ def test_bad_input_fails(tclb_bin, tmp_path):
     (tmp_path / "bad2.xml").write_text("<CLBConfig><Geometry nx='32' ny='8'></CLBConfig>")
     r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", "d2q9", "bad2.xml"], cwd=tmp_path, capture_output=True, text=True)
     assert r.returncode != 0
+
+
+def test_image_element_writes_the_colour_kernel_picture(tclb_bin, tmp_path):
+    """<Image>: the headless counterpart of the reference's interactive view (velocity magnitude through the colour map,
+    src/LatticeContainer.inc.cpp.Rt:355-423): one binary PPM per call, equal to Domain.color() of the same state"""
+    import subprocess
+    import numpy as np
+    from golden_karman import KARMAN_XML
+    xml = KARMAN_XML.replace('<Solve Iterations="1000"', '<Image Iterations="40" scale="20"/><Solve Iterations="40"')
+    (tmp_path / "k.xml").write_text(xml)
+    r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", "--ranks", "2", "d2q9", "k.xml"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    raw = open(tmp_path / "output" / "k_Image_00000040.ppm", "rb").read()
+    head, w_h, mx, rest = raw.split(b"\n", 3)
+    assert head == b"P6" and w_h == b"1024 100" and mx == b"255" and len(rest) == 1024 * 100 * 3
+    img = np.frombuffer(rest, dtype=np.uint8).reshape(100, 1024, 3)
+    assert len(np.unique(img.reshape(-1, 3), axis=0)) > 20          # a picture, not a constant
+    assert not np.array_equal(img[50, 100:200], img[50, 600:700])   # wake behind the obstacle differs from the inflow
