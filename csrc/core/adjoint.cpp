@@ -1,4 +1,5 @@
 #include "adjoint.h"
+#include <unistd.h>
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <algorithm>
@@ -70,6 +71,9 @@ Adjoint::Adjoint(Domain *dom) : dom_(dom), lat_(nullptr) {
     else if (dev) { size_t fr = 0, tot = 0; ADJ_CUDA(cudaMemGetInfo(&fr, &tot)); dev_tape_cap_ = (size_t)(0.7 * (double)fr); }
     else dev_tape_cap_ = 0;
     if (const char *f = getenv("TCLB_TAPE_FRAMES")) max_frames_ = atoi(f);
+    if (const char *h = getenv("TCLB_TAPE_HOST_BYTES")) host_tape_cap_ = (size_t)atoll(h);
+    const char *td = getenv("TCLB_TAPE_DIR");
+    tape_dir_ = td && *td ? td : (getenv("TMPDIR") ? getenv("TMPDIR") : "/tmp");
 }
 Adjoint::~Adjoint() {
     drop_tape();
@@ -119,6 +123,20 @@ Adjoint::Frame Adjoint::grab_frame(bool with_pre) {
     size_t need = 0;
     for (Sub &s : subs_) need += s.lat->snap_bytes * (with_pre ? 2 : 1);
     f.on_device = dev && dev_tape_bytes_ + need <= dev_tape_cap_;
+    f.on_disk = !f.on_device && host_tape_bytes_ + need > host_tape_cap_;
+    if (f.on_disk) {
+        for (Sub &s : subs_) {
+            std::string name;
+            frame_to_disk(s, s.lat->snap_ptr(s.lat->cur), dev, name);
+            f.data.push_back(nullptr); f.files.push_back(name);
+            if (with_pre) {
+                frame_to_disk(s, s.lat->snap_ptr(s.lat->cur ^ 1), dev, name);
+                f.pre.push_back(nullptr); f.pre_files.push_back(name);
+            }
+        }
+        return f;
+    }
+    if (!f.on_device) host_tape_bytes_ += need;
     for (Sub &s : subs_) {
         void *d = frame_get(s, f.on_device);
         copy_snap(s, d, s.lat->snap_ptr(s.lat->cur), f.on_device, dev);
@@ -132,7 +150,49 @@ Adjoint::Frame Adjoint::grab_frame(bool with_pre) {
     if (f.on_device) dev_tape_bytes_ += need;
     return f;
 }
+void Adjoint::frame_to_disk(const Sub &s, const void *snap, bool src_dev, std::string &name) {
+    void *h = frame_get(s, false);
+    copy_snap(s, h, snap, false, src_dev);
+    name = tape_dir_ + "/tclb_tape_" + std::to_string((long)getpid()) + "_" + std::to_string((long)(size_t)this % 1000003) + "_" + std::to_string(tape_file_seq_++) + ".bin";
+    FILE *fp = fopen(name.c_str(), "wb");
+    if (!fp) fail("adjoint tape: cannot write %s (TCLB_TAPE_DIR)", name.c_str());
+    const size_t n = fwrite(h, 1, s.lat->snap_bytes, fp);
+    fclose(fp);
+    frame_put(h, false, s.lat->snap_bytes);
+    if (n != s.lat->snap_bytes) fail("adjoint tape: short write to %s", name.c_str());
+}
+void Adjoint::frame_load(const Frame &f, std::vector<void *> &data, std::vector<void *> &pre) {
+    auto rd = [&](const Sub &s, const std::string &name) {
+        void *h = frame_get(s, false);
+        FILE *fp = fopen(name.c_str(), "rb");
+        if (!fp) fail("adjoint tape: cannot read %s", name.c_str());
+        const size_t n = fread(h, 1, s.lat->snap_bytes, fp);
+        fclose(fp);
+        if (n != s.lat->snap_bytes) fail("adjoint tape: short read from %s", name.c_str());
+        return h;
+    };
+    for (size_t k = 0; k < subs_.size(); k++) {
+        data.push_back(rd(subs_[k], f.files[k]));
+        if (!f.pre_files.empty()) pre.push_back(rd(subs_[k], f.pre_files[k]));
+    }
+}
+void Adjoint::frame_unload(std::vector<void *> &data, std::vector<void *> &pre) {
+    for (size_t k = 0; k < data.size(); k++) frame_put(data[k], false, subs_[k].lat->snap_bytes);
+    for (size_t k = 0; k < pre.size(); k++) frame_put(pre[k], false, subs_[k].lat->snap_bytes);
+    data.clear(); pre.clear();
+}
 void Adjoint::free_frame(Frame &f) {
+    if (f.on_disk) {
+        for (auto &n : f.files) remove(n.c_str());
+        for (auto &n : f.pre_files) remove(n.c_str());
+        f.files.clear(); f.pre_files.clear(); f.data.clear(); f.pre.clear();
+        return;
+    }
+    if (!f.on_device) {
+        size_t need = 0;
+        for (size_t k = 0; k < subs_.size(); k++) need += subs_[k].lat->snap_bytes * ((k < f.data.size() && f.data[k]) ? 1 : 0) + subs_[k].lat->snap_bytes * ((k < f.pre.size() && f.pre[k]) ? 1 : 0);
+        host_tape_bytes_ -= std::min(host_tape_bytes_, need);
+    }
     size_t k = 0;
     for (Sub &s : subs_) {
         if (k < f.data.size() && f.data[k]) { frame_put(f.data[k], f.on_device, s.lat->snap_bytes); if (f.on_device) dev_tape_bytes_ -= s.lat->snap_bytes; }
@@ -158,13 +218,17 @@ void Adjoint::frame_put(void *p, bool device, size_t bytes) {
 }
 void Adjoint::restore_frame(const Frame &f) {
     const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+    std::vector<void *> ld, lp;
+    if (f.on_disk) frame_load(f, ld, lp);
+    const std::vector<void *> &data = f.on_disk ? ld : f.data, &pre = f.on_disk ? lp : f.pre;
     for (size_t k = 0; k < subs_.size(); k++) {
         Sub &s = subs_[k];
-        copy_snap(s, s.lat->snap_ptr(s.lat->cur), f.data[k], dev, f.on_device);
-        if (!f.pre.empty()) copy_snap(s, s.lat->snap_ptr(s.lat->cur ^ 1), f.pre[k], dev, f.on_device);
+        copy_snap(s, s.lat->snap_ptr(s.lat->cur), data[k], dev, f.on_device);
+        if (!pre.empty()) copy_snap(s, s.lat->snap_ptr(s.lat->cur ^ 1), pre[k], dev, f.on_device);
         s.lat->iter = f.iter;
     }
     dom_->iter = f.iter;
+    if (f.on_disk) { lat_->sync(); frame_unload(ld, lp); }
 }
 void Adjoint::drop_tape() {
     for (Frame &f : tape_) free_frame(f);
@@ -331,8 +395,11 @@ void Adjoint::reverse_segment(const Frame &f, long len, int slots) {
         std::vector<const void *> in, pre;
         std::vector<void *> staged;
         const bool dev = lat_->backend == TCLB_BACKEND_CUDA;
+        std::vector<void *> ld, lp;
+        if (f.on_disk) frame_load(f, ld, lp);
+        const std::vector<void *> &fdata = f.on_disk ? ld : f.data, &fpre = f.on_disk ? lp : f.pre;
         for (size_t k = 0; k < subs_.size(); k++) {
-            const void *p = f.data[k], *q = multi ? f.pre[k] : nullptr;
+            const void *p = fdata[k], *q = multi ? fpre[k] : nullptr;
             if (dev && !f.on_device) {       // host frame: bring it to the device first
                 void *b = frame_get(subs_[k], true); copy_snap(subs_[k], b, p, true, false); staged.push_back(b); p = b;
                 if (multi) { void *c = frame_get(subs_[k], true); copy_snap(subs_[k], c, q, true, false); staged.push_back(c); q = c; }
@@ -341,6 +408,7 @@ void Adjoint::reverse_segment(const Frame &f, long len, int slots) {
         }
         step(in, pre, f.iter);
         for (size_t k = 0; k < staged.size(); k++) frame_put(staged[k], true, subs_[0].lat->snap_bytes);
+        if (f.on_disk) { lat_->sync(); frame_unload(ld, lp); }
         return;
     }
     if (len - 1 <= slots) {

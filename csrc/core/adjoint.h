@@ -65,10 +65,19 @@ class Adjoint {
     typedef int (*stage_fn)(int, const tclb_launch_t *, const void *, void *);
     typedef const char *(*err_fn)(void);
     // one stored state of the whole lattice: per subdomain the current snapshot (+ the other one for multi-stage actions)
-    struct Frame { std::vector<void *> data, pre; bool on_device = false; int iter = 0; long index = 0; };
+    // a stored state lives in device memory, in (page-locked) host memory, or - beyond TCLB_TAPE_HOST_BYTES - in files under
+    // TCLB_TAPE_DIR (the reference's snapshot levels end on disk the same way, src/Lattice.cu.Rt:200-233)
+    struct Frame { std::vector<void *> data, pre; bool on_device = false, on_disk = false; int iter = 0; long index = 0;
+                   std::vector<std::string> files, pre_files; };
+    size_t host_tape_bytes_ = 0, host_tape_cap_ = (size_t)-1;
+    std::string tape_dir_;
+    long tape_file_seq_ = 0;
     // per subdomain: two adjoint buffers (snapshot layout in real_t), and for multi-stage actions a scratch adjoint, the
     // adjoint left over for the previous state, and the state before every later stage
     struct Sub { Lattice *lat = nullptr; void *adj[2] = {nullptr, nullptr}; void *tmp = nullptr, *resid = nullptr; std::vector<void *> inter; size_t bytes = 0; };
+    void frame_to_disk(const Sub &s, const void *snap_dev_or_host, bool src_dev, std::string &name);
+    void frame_load(const Frame &f, std::vector<void *> &data, std::vector<void *> &pre);     // host staging copies of an on-disk frame
+    void frame_unload(std::vector<void *> &data, std::vector<void *> &pre);
     Domain *dom_;
     Lattice *lat_;
     std::vector<Sub> subs_;

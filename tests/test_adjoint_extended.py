@@ -245,3 +245,35 @@ def test_pf_velocity_adjoint_against_finite_differences(built, reference_dir, nr
     assert len(phys) >= 27 + 15 + 4
     _terminal_check(d, m, 3, 1e-7, fields=phys)
     d.close()
+
+
+def test_tape_spills_to_disk_and_gives_the_same_gradient(built, tmp_path, monkeypatch):
+    """TCLB_TAPE_HOST_BYTES bounds the host part of the tape; the frames beyond it are files under TCLB_TAPE_DIR (the
+    reference's snapshot levels end on disk too, src/Lattice.cu.Rt:200-233): same gradient, files removed afterwards"""
+    build.build_model_lib("d2q9", "double")
+    build.build_adjoint_lib("d2q9", "double")
+    m = Model("d2q9", "double")
+
+    def gradient():
+        d = _channel(m, (24, 16, 1))
+        d.set_setting("Viscosity", 0.05); d.set_setting("GravitationX", 1e-4)
+        d.set_setting("OutletFluxInObj", 1.0)
+        fl = d.get_flags(); fl[:, 1:-1, -4] |= m.flag("Outlet"); d.set_flags(fl)
+        d.init(); d.iterate(5)
+        adj = Adjoint(d)
+        adj.record(20)
+        seen = sorted(os.listdir(tmp_path))
+        adj.reverse()
+        g = {f: adj.get_field(f) for f in m.fields}
+        adj.close(); d.close()
+        return g, seen
+
+    monkeypatch.setenv("TCLB_TAPE_DIR", str(tmp_path))
+    in_memory, seen = gradient()
+    assert seen == []
+    monkeypatch.setenv("TCLB_TAPE_HOST_BYTES", str(3 * 24 * 18 * 9 * 8))      # room for about three frames in memory
+    spilled, seen = gradient()
+    assert len(seen) >= 15 and all(n.startswith("tclb_tape_") for n in seen)
+    assert sorted(os.listdir(tmp_path)) == []                                  # every file removed when its frame was released
+    for f in in_memory:
+        assert np.array_equal(in_memory[f], spilled[f]), f
