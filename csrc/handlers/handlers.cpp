@@ -523,12 +523,13 @@ class CbVTK : public Callback {
 TCLB_REGISTER_HANDLER("VTK", CbVTK)
 
 // <HDF5 name what compress write_xdmf point_data precision dx..nz> (reference cbHDF5.cpp): one .h5 for the whole output
-// region + an .xmf index.  `compress` and `chunk` are accepted and ignored (the built-in writer stores contiguous data).
+// region + an .xmf index.  `compress` (true or a level 1..9) stores every dataset chunked (slabs along z) with the deflate filter; `chunk` is accepted and ignored.
 class CbHDF5 : public Callback {
     std::string nm;
     NameSet what;
     Box reg;
     bool xdmf = true, point = false, dbl = false;
+    int deflate = 0;
   public:
     int init() override {
         Callback::init();
@@ -542,10 +543,13 @@ class CbHDF5 : public Callback {
         if (pr == "double") dbl = true;
         else if (pr == "float" || pr.empty()) dbl = false;
         else { logf(L_ERROR, "HDF5: precision should be float or double"); return -1; }
-        if (node->has_attr("compress") && node->attr_bool("compress")) logf(L_WARNING, "HDF5: compress is ignored, the data are stored contiguously");
+        if (node->has_attr("compress")) {      // true/false, or a deflate level 1..9 (reference cbHDF5.cpp:102-127: deflate on chunked datasets)
+            const std::string c = node->attr("compress");
+            deflate = (c.size() == 1 && c[0] >= '0' && c[0] <= '9') ? c[0] - '0' : (node->attr_bool("compress") ? 6 : 0);
+        }
         return 0;
     }
-    int do_it() override { return solver->write_hdf5(nm, what, reg, dbl, xdmf, point); }
+    int do_it() override { return solver->write_hdf5(nm, what, reg, dbl, xdmf, point, deflate); }
 };
 TCLB_REGISTER_HANDLER("HDF5", CbHDF5)
 

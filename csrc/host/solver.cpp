@@ -297,7 +297,7 @@ int Solver::write_vtk(const std::string &name, const NameSet &what, const Box &r
 
 // <HDF5>: one file for the whole output region (reference src/hdf5Lattice.cpp:26-339: datasets [nz][ny][nx] or
 // [nz][ny][nx][3], one per node-type group and quantity, values in SI units; .xmf = 3DCoRectMesh index)
-int Solver::write_hdf5(const std::string &name, const NameSet &what, const Box &region_out, bool as_double, bool write_xdmf, bool point_data) {
+int Solver::write_hdf5(const std::string &name, const NameSet &what, const Box &region_out, bool as_double, bool write_xdmf, bool point_data, int deflate) {
     logf(L_OUTPUT, "%8d it writing hdf5", iter);
     const tclb_model_t *d = model->d;
     // Every subdomain in this process: ONE file of the whole region (what the reference's collective write produces,
@@ -343,7 +343,7 @@ int Solver::write_hdf5(const std::string &name, const NameSet &what, const Box &
             const tclb_nodegroup_t &G = d->nodegroups[g];
             if (!((what.all && G.save) || what.explicitly_in(G.name))) continue;
             for (size_t i = 0; i < N; i++) small[i] = (unsigned char)((flags[i] & G.mask) >> G.shift);
-            h5.add(G.name, H5MinWriter::U8, {(uint64_t)out.nz, (uint64_t)out.ny, (uint64_t)out.nx}, small.data());
+            h5.add(G.name, H5MinWriter::U8, {(uint64_t)out.nz, (uint64_t)out.ny, (uint64_t)out.nx}, small.data(), deflate);
             xdmf_attr(G.name, 1, 1, "UChar");
         }
         for (int q = 0; q < d->n_quantities; q++) {
@@ -365,8 +365,8 @@ int Solver::write_hdf5(const std::string &name, const NameSet &what, const Box &
             }
             std::vector<uint64_t> dims = {(uint64_t)out.nz, (uint64_t)out.ny, (uint64_t)out.nx};
             if (comp == 3) dims.push_back(3);
-            if (as_double) h5.add(d->quantities[q].name, H5MinWriter::F64, dims, full.data());
-            else { std::vector<float> f32(full.begin(), full.end()); h5.add(d->quantities[q].name, H5MinWriter::F32, dims, f32.data()); }
+            if (as_double) h5.add(d->quantities[q].name, H5MinWriter::F64, dims, full.data(), deflate);
+            else { std::vector<float> f32(full.begin(), full.end()); h5.add(d->quantities[q].name, H5MinWriter::F32, dims, f32.data(), deflate); }
             xdmf_attr(d->quantities[q].name, comp, as_double ? 8 : 4, "Float");
         }
         h5.write(file);

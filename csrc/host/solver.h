@@ -94,7 +94,7 @@ class Solver {
     void write_log(const std::string &filename);
     int write_vtk(const std::string &name, const NameSet &what, const Box &region);
     int write_txt(const std::string &name, const NameSet &what, bool gzip);
-    int write_hdf5(const std::string &name, const NameSet &what, const Box &region, bool as_double, bool write_xdmf, bool point_data);
+    int write_hdf5(const std::string &name, const NameSet &what, const Box &region, bool as_double, bool write_xdmf, bool point_data, int deflate = 0);
     int write_bin(const std::string &name);
     void save_solution(const std::string &prefix, std::vector<std::string> *files = nullptr);
     void load_solution(const std::string &prefix);

@@ -31,7 +31,7 @@ ELEMENTS = {
     "Container": ("container", "", "grouping"),
     "EvalIf": ("container", "opt_present opt_missing", "children run only if the model has / lacks an option"),
     "VTK": ("callback", "Iterations name what dx dy dz nx ny nz", "ImageData pieces + .pvti index"),
-    "HDF5": ("callback", "Iterations name what compress write_xdmf point_data precision dx dy dz nx ny nz", "one .h5 for the output region + .xmf (3DCoRectMesh) index; one process per GPU: one piece per rank + an XDMF spatial collection"),
+    "HDF5": ("callback", "Iterations name what compress write_xdmf point_data precision dx dy dz nx ny nz", "one .h5 for the output region + .xmf (3DCoRectMesh) index; compress=true|1..9: chunked datasets with deflate; one process per GPU: one piece per rank + an XDMF spatial collection"),
     "TXT": ("callback", "Iterations name what gzip", "one text file per quantity"),
     "Image": ("callback", "Iterations name plane scale", "the picture of the reference's interactive view (colour kernel of one z-plane) as a binary PPM"),
     "BIN": ("callback", "Iterations name", "raw binary per quantity"),

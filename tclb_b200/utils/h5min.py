@@ -1,5 +1,5 @@
 """Reader for the HDF5 subset written by csrc/io/h5min.cpp (and by libhdf5 for plain contiguous datasets in a
-version-0/1 file): superblock v0, v1 object headers, group B-tree + local heap + symbol-table nodes, contiguous layout,
+version-0/1 file): superblock v0, v1 object headers, group B-tree + local heap + symbol-table nodes, contiguous layout or chunked layout (version-1 chunk B-tree) with the deflate filter,
 little-endian IEEE floats and integers.  Follows the structures, i.e. it fails on an inconsistent file; used by the
 tests and handy where h5py is missing.  ``read(path) -> {name: ndarray}``."""
 from __future__ import annotations
@@ -89,21 +89,78 @@ def read(path: str) -> Dict[str, np.ndarray]:
                 assert name_at(_u(b, p + 16, 8)) == names[-1], "B-tree key is not the last name of its child"
             p += 16
 
+    def _chunks(node, rank, out_list):
+        """version-1 B-tree of raw data chunks: (offsets, address, stored size, filter mask) of every chunk, in key order"""
+        assert b[node:node + 4] == b"TREE" and b[node + 4] == 1, "chunk B-tree node"
+        level, used = b[node + 5], _u(b, node + 6, 2)
+        assert used <= 64, "more entries than a node of K = 32 holds"
+        ksz = 8 + 8 * (rank + 1)
+        p = node + 24
+        for i in range(used):
+            size, mask = _u(b, p, 4), _u(b, p + 4, 4)
+            offs = [_u(b, p + 8 + 8 * d, 8) for d in range(rank + 1)]
+            child = _u(b, p + ksz, 8)
+            if level > 0:
+                _chunks(child, rank, out_list)
+            else:
+                out_list.append((offs, child, size, mask))
+            p += ksz + 8
+
     def _dataset(hdr):
-        dims = dt = addr = nbytes = None
+        import zlib
+        dims = dt = addr = nbytes = chunk = None
+        filters = []
         for t, m in _messages(b, hdr):
             if t == 1:
                 assert m[0] == 1
                 dims = [_u(m, 8 + 8 * i, 8) for i in range(m[1])]
             elif t == 3:
                 dt = _dtype(m)
+            elif t == 0x0B:
+                assert m[0] == 1, "filter pipeline version 1 expected"
+                off = 8
+                for _ in range(m[1]):
+                    fid, nlen, flags, ncl = struct.unpack_from("<HHHH", m, off)
+                    off += 8 + ((nlen + 7) // 8) * 8
+                    vals = [_u(m, off + 4 * i, 4) for i in range(ncl)]
+                    off += 4 * ncl + (4 if ncl % 2 else 0)
+                    filters.append((fid, vals))
             elif t == 8:
-                assert m[0] == 3 and m[1] == 1, "contiguous layout version 3 expected"
-                addr, nbytes = _u(m, 2, 8), _u(m, 10, 8)
+                assert m[0] == 3, "layout version 3 expected"
+                if m[1] == 1:
+                    addr, nbytes = _u(m, 2, 8), _u(m, 10, 8)
+                elif m[1] == 2:
+                    nd = m[2]
+                    addr = _u(m, 3, 8)
+                    chunk = [_u(m, 11 + 4 * i, 4) for i in range(nd)]
+                else:
+                    raise ValueError("layout class %d not supported" % m[1])
         assert dims is not None and dt is not None and addr is not None, "dataset header incomplete"
         n = int(np.prod(dims)) if dims else 1
-        assert nbytes == n * dt.itemsize and addr + nbytes <= len(b), "data extent"
-        return np.frombuffer(b, dtype=dt, count=n, offset=addr).reshape(dims).copy()
+        if chunk is None:
+            assert nbytes == n * dt.itemsize and addr + nbytes <= len(b), "data extent"
+            return np.frombuffer(b, dtype=dt, count=n, offset=addr).reshape(dims).copy()
+        rank = len(dims)
+        assert len(chunk) == rank + 1 and chunk[-1] == dt.itemsize, "chunk dimensions"
+        assert all(f[0] == 1 for f in filters), "only the deflate filter is supported"
+        out_arr = np.zeros(dims, dtype=dt)
+        lst = []
+        _chunks(addr, rank, lst)
+        assert [c[0] for c in lst] == sorted(c[0] for c in lst), "chunk keys are not ordered"
+        for offs, caddr, size, mask in lst:
+            raw = b[caddr:caddr + size]
+            assert len(raw) == size, "chunk beyond the end of the file"
+            if filters and not (mask & 1):
+                raw = zlib.decompress(raw)
+            shape = chunk[:-1]
+            assert len(raw) == int(np.prod(shape)) * dt.itemsize, "chunk size after the filters"
+            blk = np.frombuffer(raw, dtype=dt).reshape(shape)
+            sl_out = tuple(slice(offs[d], min(offs[d] + shape[d], dims[d])) for d in range(rank))
+            sl_in = tuple(slice(0, s_.stop - s_.start) for s_ in sl_out)
+            out_arr[sl_out] = blk[sl_in]
+        covered = sum(min(c[0][0] + chunk[0], dims[0]) - c[0][0] for c in lst)
+        assert covered == dims[0], "the chunks do not cover the dataset"
+        return out_arr
 
     walk(btree)
     return out
