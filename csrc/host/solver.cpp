@@ -111,7 +111,7 @@ void Solver::read_units() {
         i++;
     }
     units.make_gauge();
-    if (is_root() || !domain) units.print_gauge();
+    if (!domain || is_root()) units.print_gauge();
 }
 
 void Solver::set_size(int nx, int ny, int nz) {

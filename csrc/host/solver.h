@@ -83,7 +83,8 @@ class Solver {
     void read_units();
     void set_size(int nx, int ny, int nz);
     void set_output(const std::string &out);
-    int first_rank() const { return domain->local[0]; }
+    // before the lattice exists (reading <Units>, naming the output) the first local rank is the one asked for on the command line
+    int first_rank() const { return domain && !domain->local.empty() ? domain->local[0] : (opt.local_ranks.empty() ? 0 : opt.local_ranks[0]); }
     bool is_root() const { return first_rank() == 0; }
     // ---- file names ----
     std::string out_iter_file(const std::string &name, const std::string &suffix, int rank = -1) const;

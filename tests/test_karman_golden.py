@@ -116,3 +116,33 @@ def test_image_element_writes_the_colour_kernel_picture(tclb_bin, tmp_path):
     img = np.frombuffer(rest, dtype=np.uint8).reshape(100, 1024, 3)
     assert len(np.unique(img.reshape(-1, 3), axis=0)) > 20          # a picture, not a constant
     assert not np.array_equal(img[50, 100:200], img[50, 600:700])   # wake behind the obstacle differs from the inflow
+
+
+def test_case_with_units_element_runs_from_the_command_line(tclb_bin, tmp_path):
+    """a case in physical units (the reference's example/flow/2d/D2Q9_Poiseuille.xml pattern): <Units> is read before the
+    lattice exists; the gauge is printed and lengths / viscosities are converted"""
+    import subprocess
+    xml = """<?xml version="1.0"?>
+<CLBConfig version="2.0" output="output/" permissive="true">
+  <Units>
+    <Param name="size" value="0.0005m" gauge="1"/>
+    <Param name="nu" value="1e-5m2/s" gauge="0.1666666666"/>
+  </Units>
+  <Geometry nx="0.02m" ny="0.0105m">
+    <MRT><Box/></MRT>
+    <Wall mask="ALL"><Channel/></Wall>
+  </Geometry>
+  <Model>
+    <Param name="Viscosity" value="1e-5m2/s"/>
+    <Param name="GravitationX" value="1e-4m/s2"/>
+  </Model>
+  <Log Iterations="5"/>
+  <Solve Iterations="10"/>
+</CLBConfig>
+"""
+    (tmp_path / "u.xml").write_text(xml)
+    r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", "d2q9", "u.xml"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    out = r.stdout + r.stderr
+    assert r.returncode == 0, out[-2000:]
+    assert "GAUGE" in out and "Global lattice size: 40x21x1" in out
+    assert "0.1666" in out and "1 s = 240.000000 units" in out          # 1e-5 m2/s in lattice units; the time scale that follows
