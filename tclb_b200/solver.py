@@ -295,7 +295,7 @@ class Solver:
         """<RunR> without R: the block runs in this repository's R-subset interpreter (tclb_b200/gen/rinterp.py, the one that
         executes the models' Dynamics.R) with a `Solver` list of the same shape the reference's RInside bridge offers
         (src/Handlers/cbRunR.cpp:484-520, 751-845): Solver$Settings$<name>, Solver$Globals$<name>, Solver$Quantities$<name>,
-        Solver$Fields$<name>, Solver$Geometry$X|Y|Z, Solver$Geometry$<GROUP> (node-type names per node), Solver$Iteration.  Lattice arrays are vectors in the lattice's memory
+        Solver$Fields$<name>, Solver$Geometry$X|Y|Z, Solver$Geometry$<GROUP> (node-type names per node), Solver$Actions$<name>(), Solver$Iteration.  Lattice arrays are vectors in the lattice's memory
         order (x fastest; a vector quantity is 3 x nodes).  Only what the block mentions is materialised; after the block,
         fields, settings and node types it changed are written back.  The language coverage is the interpreter's (vector arithmetic,
         data frames, apply-family, control flow, write.csv), not all of R."""
@@ -345,38 +345,75 @@ class Solver:
         I = getattr(self, "_r_interp", None)
         if I is None:
             I = self._r_interp = Interp()
+        nx, ny, nz = d.shape
+
+        def flush():
+            """what the R code changed so far goes to the lattice (end of the block, and before an action it calls)"""
+            S2 = I.globals.get("Solver")
+            for k, v in S2["Fields"].items():
+                a = np.asarray(v, dtype=np.float64).ravel()
+                if k not in m.fields:
+                    raise RuntimeError(f"<RunR>: the model has no field {k}")
+                if k not in before_fields or a.shape != before_fields[k].shape or not np.array_equal(a, before_fields[k]):
+                    d.set_field(k, np.resize(a, nx * ny * nz).reshape(nz, ny, nx))
+                    before_fields[k] = np.resize(a, nx * ny * nz).copy()
+            for k, old_names in before_groups.items():
+                now = np.array([str(x) for x in np.asarray(S2["Geometry"][k], dtype=object).ravel()], dtype=object)
+                if now.shape != old_names.shape:
+                    raise RuntimeError(f"<RunR>: Solver$Geometry${k} changed its length")
+                changed = now != old_names
+                if changed.any():
+                    fl = geo.flags()
+                    flat = fl.reshape(-1)
+                    mask = np.uint32(m.nodegroups[k][0])
+                    for name in sorted(set(now[changed].tolist())):
+                        if name not in ("None", "") and (name not in m.nodetypes or m.nodetypes[name][1] != int(mask)):
+                            raise RuntimeError(f"<RunR>: {name} is not a node type of group {k}")
+                        val = np.uint32(0 if name in ("None", "") else m.nodetypes[name][0])
+                        sel = changed & (now == name)
+                        flat[sel] = (flat[sel] & ~mask) | val
+                    d.set_flags(fl)
+                    before_groups[k] = now
+            for k, v in S2["Settings"].items():
+                x = float(np.asarray(v).ravel()[0])
+                if k not in before_settings:
+                    raise RuntimeError(f"<RunR>: the model has no setting {k}")
+                if x != before_settings[k]:
+                    d.set_setting(k, x)
+                    before_settings[k] = x
+
+        def refresh():
+            """after an action: the fields and quantities the block holds show the new state"""
+            S2 = I.globals.get("Solver")
+            for k in list(S2["Fields"].keys()):
+                S2["Fields"][k] = np.asarray(d.get_field(k), dtype=np.float64).ravel()
+                before_fields[k] = np.array(S2["Fields"][k], copy=True)
+            for k in list(S2["Quantities"].keys()):
+                a = d.get_quantity(k)
+                S2["Quantities"][k] = np.ascontiguousarray(a, dtype=np.float64).reshape(-1, 3).T.copy() if m.quantities[k] else np.asarray(a, dtype=np.float64).ravel()
+
+        # Solver$Actions$<name>(): Init, Iterate(n) and the model's actions (e.g. InitFromFields), applied to what the block wrote so far
+        acts = RList()
+
+        def make_action(name):
+            def run(I_, a, k):
+                flush()
+                if name == "Iterate":
+                    d.iterate(int(np.asarray(a[0]).ravel()[0]) if a else 1)
+                elif name == "Init":
+                    d.init()
+                else:
+                    d.run_action(name)
+                refresh()
+                from .gen.rlang import NULL
+                return NULL
+            return run
+        for name in ["Iterate", "Init"] + [a_ for a_ in m.actions if a_ not in ("Iteration", "Init")]:
+            acts[name] = make_action(name)
+        S["Actions"] = acts
         I.globals.set("Solver", S)
         I.run(src, I.globals)
-        S2 = I.globals.get("Solver")
-        nx, ny, nz = d.shape
-        for k, v in S2["Fields"].items():
-            a = np.asarray(v, dtype=np.float64).ravel()
-            if k not in m.fields:
-                raise RuntimeError(f"<RunR>: the model has no field {k}")
-            if k not in before_fields or a.shape != before_fields[k].shape or not np.array_equal(a, before_fields[k]):
-                d.set_field(k, np.resize(a, nx * ny * nz).reshape(nz, ny, nx))
-        for k, old_names in before_groups.items():
-            now = np.array([str(x) for x in np.asarray(S2["Geometry"][k], dtype=object).ravel()], dtype=object)
-            if now.shape != old_names.shape:
-                raise RuntimeError(f"<RunR>: Solver$Geometry${k} changed its length")
-            changed = now != old_names
-            if changed.any():
-                fl = geo.flags()
-                flat = fl.reshape(-1)
-                mask = np.uint32(m.nodegroups[k][0])
-                for name in sorted(set(now[changed].tolist())):
-                    if name not in ("None", "") and (name not in m.nodetypes or m.nodetypes[name][1] != int(mask)):
-                        raise RuntimeError(f"<RunR>: {name} is not a node type of group {k}")
-                    val = np.uint32(0 if name in ("None", "") else m.nodetypes[name][0])
-                    sel = changed & (now == name)
-                    flat[sel] = (flat[sel] & ~mask) | val
-                d.set_flags(fl)
-        for k, v in S2["Settings"].items():
-            x = float(np.asarray(v).ravel()[0])
-            if k not in before_settings:
-                raise RuntimeError(f"<RunR>: the model has no setting {k}")
-            if x != before_settings[k]:
-                d.set_setting(k, x)
+        flush()
 
     # ---- <RunPython> ----
     def _on_script(self, user, element, code, iteration) -> int:
