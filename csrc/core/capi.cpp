@@ -75,8 +75,12 @@ int tclb_domain_set_setting(tclb_domain_h *h, const char *name, double v) {
 }
 double tclb_domain_get_setting(tclb_domain_h *h, const char *name) {
     int i = h->d->model->find_setting(name);
+    if (i >= 0) return h->d->lat[h->d->local[0]]->get_setting(i);
+    // a zonal setting: its value in the default zone at the current time level
+    i = h->d->model->find_zonesetting(name);
     if (i < 0) return NAN;
-    return h->d->lat[h->d->local[0]]->get_setting(i);
+    Lattice *l = h->d->lat[h->d->local[0]];
+    return l->zs.get(i, 0, l->zs.len() > 1 ? l->iter % l->zs.len() : 0);
 }
 int tclb_domain_set_zone_setting(tclb_domain_h *h, const char *name, int zone, double v) {
     GUARD_BEGIN

@@ -378,7 +378,7 @@ class Solver:
                 x = float(np.asarray(v).ravel()[0])
                 if k not in before_settings:
                     raise RuntimeError(f"<RunR>: the model has no setting {k}")
-                if x != before_settings[k]:
+                if x != before_settings[k] and not (x != x and before_settings[k] != before_settings[k]):     # NaN stays NaN: not a change
                     d.set_setting(k, x)
                     before_settings[k] = x
 

@@ -64,3 +64,33 @@ def test_d2q9_kuper_drop_initial_density_matches_golden_stats(reference_dir, bui
     assert got[0] == gold[0] == '"max","min"'
     for a, b in zip(got[1].split(","), gold[1].split(",")):
         assert abs(float(a) - float(b)) < 1e-12, (got[1], gold[1])
+
+
+def test_reference_runr_example_allen_cahn(reference_dir, built, tmp_path, monkeypatch):
+    """example/reaction/d2q9_AllenCahn_SourceTerm_SOI_runr.xml with its own <RunR> block (coordinates, three external
+    initialisation fields written from R expressions, Solver$Actions$InitFromFields()) on a smaller lattice: the phase field
+    follows exp(sin(2 pi x)) + 2 exp(sin(4 pi y)) (smoothed by the model) after the block and stays finite over the iterations"""
+    import numpy as np
+    from tclb_b200 import build
+    from tclb_b200.solver import Solver
+    build.build_from_dir(os.path.join(reference_dir, "models/reaction/d2q9_AllenCahn_SourceTerm_SOI"), precision="double")
+    xml = open(os.path.join(reference_dir, "example/reaction/d2q9_AllenCahn_SourceTerm_SOI_runr.xml")).read()
+    assert "Solver$Actions$InitFromFields()" in xml
+    xml = re.sub(r'nx="\d+"', 'nx="64"', xml, count=1)
+    xml = re.sub(r'ny="\d+"', 'ny="64"', xml, count=1)
+    no_iter = re.sub(r"<Solve Iterations=.*?</Solve>", "", xml, flags=re.S)
+    monkeypatch.chdir(tmp_path)
+    s = Solver("ref_d2q9_AllenCahn_SourceTerm_SOI", "double", "cpu")
+    s.load_string(no_iter, "ac0").run()
+    x = np.arange(64) / 63.0
+    want = np.exp(np.sin(2 * np.pi * x))[None, :] + 2 * np.exp(np.sin(4 * np.pi * x))[:, None]
+    got = s.domain.get_quantity("PhaseField")[0]
+    # the model's InitFromFields smooths the external field a little (phase_field_smoothing_coeff): compare shapes
+    assert np.corrcoef(got.ravel(), want.ravel())[0, 1] > 0.995 and np.abs(got - want).max() < 0.6
+    assert s.domain.get_setting("Init_PhaseField") == 1.0            # zonal settings read back as numbers, not NaN
+    s.close()
+    s = Solver("ref_d2q9_AllenCahn_SourceTerm_SOI", "double", "cpu")
+    s.load_string(re.sub(r'Iterations="\d+"', 'Iterations="5"', xml), "ac1").run()
+    a = s.domain.get_quantity("PhaseField")
+    assert np.isfinite(a).all() and a.max() > 2.0
+    s.close()
