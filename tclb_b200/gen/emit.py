@@ -1171,7 +1171,8 @@ TCLB_HD void halo_put(const KArgs &a, int fi, int x, int y, int z, storage_t v) 
     A("};")
     A("const tclb_nodegroup_t t_nodegroups[] = {")
     for g in m.nodetypegroups:
-        A(f"    {{{_cstr(g.name)}, {g.mask}u, {g.shift}, {g.bits}, {g.capacity}, {int(g.save)}}},")
+        # capacity is an int in the ABI: the catch-all group of a 32-bit flag word holds 2^32 - 1, reported as INT_MAX
+        A(f"    {{{_cstr(g.name)}, {g.mask}u, {g.shift}, {g.bits}, {min(int(g.capacity), 2147483647)}, {int(g.save)}}},")
     A("};")
     stage_index = {s.name: i for i, s in enumerate(m.stages)}
     for si, s in enumerate(m.stages):

@@ -123,3 +123,18 @@ def test_older_model_idioms_build_and_run(reference_dir, built):
     d.close()
     src = build.build_from_dir(os.path.join(reference_dir, "models/flow/d2q9_par"), precision="double")
     assert os.path.exists(str(src))
+
+
+def test_wide_flag_model_builds_and_runs_its_example(reference_dir, built, tclb_bin, tmp_path):
+    """heat/d2q9q9_cm_cht needs a 32-bit flag word (8 node-type groups + zones): the library builds with nvcc (the catch-all
+    group's capacity does not fit an int) and the reference's lid-driven cavity example runs"""
+    import re
+    from tclb_b200 import build
+    from tclb_b200.runtime import Model
+    build.build_from_dir(os.path.join(reference_dir, "models/heat/d2q9q9_cm_cht"), precision="double")
+    m = Model("ref_d2q9q9_cm_cht", "double")
+    assert m.flag_dtype.__name__ == "uint32"
+    xml = open(os.path.join(reference_dir, "example/heat/d2q9q9_lid_driven_cavity.xml")).read()
+    (tmp_path / "c.xml").write_text(re.sub(r'Iterations="\d+"', 'Iterations="4"', xml))
+    r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", "ref_d2q9q9_cm_cht", "c.xml"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
