@@ -247,7 +247,8 @@ void Adjoint::set_tape_frames(int n) { max_frames_ = n; }
 void Adjoint::record(int n) {
     const int obj = dom_->model->find_global("Objective");
     const bool multi = stages_.size() > 1;
-    if (tape_.empty()) { if (!zg_which_.empty()) clear_zone_gradients(); tape_count_ = 0; stride_ = 1; }
+    if (tape_.empty()) { if (!zg_which_.empty()) clear_zone_gradients(); tape_count_ = 0; stride_ = 1; integrated.clear(); }
+    bool first = integrated.empty();
     for (int i = 0; i < n; i++) {
         const long g = tape_count_++;
         if (max_frames_ <= 1 || g % stride_ == 0) {
@@ -263,7 +264,17 @@ void Adjoint::record(int n) {
         }
         dom_->iterate(1, false, true);
         if (obj >= 0) objective += dom_->globals[obj];
+        // Globals of a recorded segment are integrated over its iterations (reference ITER_INTEG, src/Lattice.h.Rt:29,
+        // calcGlobals src/Lattice.cu.Rt:1313): sums add up, maxima take the maximum
+        const int ng = dom_->model->d->n_globals;
+        if ((int)integrated.size() != ng) integrated.assign(ng, 0.0);
+        for (int k = 0; k < ng; k++) {
+            if (dom_->model->d->globals[k].op == TCLB_OP_MAX) integrated[k] = first ? dom_->globals[k] : std::max(integrated[k], dom_->globals[k]);
+            else integrated[k] = (first ? 0.0 : integrated[k]) + dom_->globals[k];
+        }
+        first = false;
     }
+    if (n > 0) for (size_t k = 0; k < integrated.size(); k++) dom_->globals[k] = integrated[k];
 }
 
 // ---- one reverse step: adj <- J^T adj + dObjective, for the iteration whose input state is in `in` (per subdomain) ----

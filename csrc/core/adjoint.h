@@ -31,6 +31,7 @@ class Adjoint {
     void steady(int n);          // n adjoint iterations around the current state (input of the next primal iteration)
     // ---- access ----
     double objective = 0.0;      // sum over the recorded iterations of the Objective global
+    std::vector<double> integrated;   // every Global integrated over the recorded iterations (SUM: sum, MAX: maximum)
     void zero();
     void get_field(int field, void *dst_real) const;    // interior [nz][ny][nx] of the adjoint of `field`, in real_t
     void set_field(int field, const void *src_real);    // seed (e.g. d(cost)/d(final state))

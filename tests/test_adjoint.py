@@ -205,3 +205,30 @@ def test_adjoint_3d_periodic_fold_matches_finite_differences_cpu():
     assert J0 != 0.0 and abs(fd - predicted) <= 1e-6 * max(abs(fd), abs(predicted)), (fd, predicted)
     adj.close()
     d.close()
+
+
+def test_recorded_segment_reports_time_integrated_globals_cpu():
+    """Globals read after a recorded segment are integrated over its iterations, like the reference's ITER_INTEG
+    (src/Lattice.h.Rt:29; calcGlobals adds the device totals of every iteration, src/Lattice.cu.Rt:1313)."""
+    build.build_model_lib("d2q9", "double")
+    build.build_adjoint_lib("d2q9", "double")
+    m = Model("d2q9", "double")
+    d = _channel(m, (24, 12, 1), "cpu")
+    base = {f: d.get_field(f).astype(np.float64) for f in m.fields}
+    n = 5
+    sums = {}
+    for _ in range(n):
+        d.iterate(1, globals_every=True)
+        for k, v in d.globals().items():
+            sums[k] = sums.get(k, 0.0) + v
+    for f in m.fields:
+        d.set_field(f, base[f])
+    adj = Adjoint(d)
+    adj.record(2)
+    adj.record(n - 2)              # two calls inside one tape keep integrating
+    got = d.globals()
+    for k in ("Objective", "OutletFlux", "PressureLoss"):
+        assert abs(got[k] - sums[k]) <= 1e-10 * max(1.0, abs(sums[k])), (k, got[k], sums[k])
+    assert abs(adj.objective - sums["Objective"]) <= 1e-10 * max(1.0, abs(sums["Objective"]))
+    adj.close()
+    d.close()
