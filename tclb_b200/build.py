@@ -200,11 +200,12 @@ def build_model_lib(variant: str, precision: str = "float", force: bool = False,
 _CUSTOM_MODELS: dict = {}      # library name -> how to load its ModelDef again (models built from a directory)
 
 
-def build_adjoint_lib(variant: str, precision: str = "double", dirs: Optional[int] = None, force: bool = False) -> Path:
+def build_adjoint_lib(variant: str, precision: str = "double", dirs: Optional[int] = None, force: bool = False, check_only: bool = False) -> Optional[Path]:
     """The adjoint companion of a model library: the same generated source compiled with -DTCLB_AD (node code in dual
     numbers, csrc/kernels/tclb_dual.h), exporting ``tclb_model_adjoint_stage``.  The runtime loads
     ``libtclb_<variant>_<precision>_ad.so`` next to the primal library when an adjoint is asked for.  `variant` is a
-    native model name or the name of an already generated source (``ref_<model>`` after build_from_dir)."""
+    native model name or the name of an already generated source (``ref_<model>`` after build_from_dir).
+    ``check_only``: compile nothing; return the library if it matches the source the generator emits now, else None."""
     if precision not in ("float", "double"):
         raise ValueError("adjoint libraries use plain float/double storage")
     LIBDIR.mkdir(parents=True, exist_ok=True)
@@ -231,6 +232,8 @@ def build_adjoint_lib(variant: str, precision: str = "double", dirs: Optional[in
     digest = _hash([src] + hdrs, precision + " ".join(NVCC_FLAGS + ARCH_FLAGS + extra))
     if not force and _stamp_ok(target, digest):
         return target
+    if check_only:
+        return None
     cmd = [NVCC] + ARCH_FLAGS + NVCC_FLAGS + extra + ["-shared", "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "kernels")]
     cmd += precision_flags(precision)
     cmd += ["-o", str(target), str(src), "-lgomp"]
