@@ -6,6 +6,7 @@ import csv
 import os
 import subprocess
 
+import numpy as np
 import pytest
 
 from golden_karman import KARMAN_IT1000, KARMAN_XML
@@ -138,3 +139,37 @@ def test_wide_flag_model_builds_and_runs_its_example(reference_dir, built, tclb_
     (tmp_path / "c.xml").write_text(re.sub(r'Iterations="\d+"', 'Iterations="4"', xml))
     r = subprocess.run([tclb_bin, "--cpu", "--precision", "double", "ref_d2q9q9_cm_cht", "c.xml"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_cm_cht_cavity_keeps_a_uniform_temperature(reference_dir, built, tmp_path, monkeypatch):
+    """heat/d2q9q9_cm_cht on its own lid-driven cavity example (example/heat/d2q9q9_lid_driven_cavity.xml, smaller box): with
+    the lid at rest the uniform state is stationary to rounding; with the lid moving a flow develops, mass is conserved and the
+    temperature (enthalpy lattice / density / cp) stays at its uniform initial value away from the lid corners"""
+    import re
+    from tclb_b200 import build
+    from tclb_b200.solver import Solver
+    build.build_from_dir(os.path.join(reference_dir, "models/heat/d2q9q9_cm_cht"), precision="double")
+    xml = open(os.path.join(reference_dir, "example/heat/d2q9q9_lid_driven_cavity.xml")).read()
+    xml = xml[xml.index("<?xml"):]
+    xml = xml.replace('nx="256" ny="256"', 'nx="48" ny="48"').replace('<Box dx="37" dy="107" nx="50" ny="50"/>', '<Box dx="10" dy="20" nx="8" ny="8"/>')
+    xml = re.sub(r'<Solve Iterations="3">.*?</Solve>', '', xml, flags=re.S)
+    xml = re.sub(r'<Failcheck[^>]*/>', '', xml)
+    xml = re.sub(r'<Solve Iterations="50000">.*?</Solve>', '<Solve Iterations="600"/>', xml, flags=re.S)
+    assert 'Iterations="600"' in xml
+    monkeypatch.chdir(tmp_path)
+
+    def run(lid):
+        s = Solver("ref_d2q9q9_cm_cht", "double", "cpu")
+        s.load_string(xml.replace('name="VelocityX" value="0.0001"', f'name="VelocityX" value="{lid}"'), "cht").run()
+        T, U, R = (np.asarray(s.Quantities[k]) for k in ("T", "U", "Rho"))
+        s.close()
+        return T[0], U[0], R[0]
+
+    T, U, R = run(0)
+    assert np.abs(T - 10).max() < 1e-12 and np.abs(U).max() < 1e-14 and np.abs(R - 1).max() < 1e-14
+    T, U, R = run(1e-4)
+    assert 5e-5 < np.abs(U).max() < 2e-4                         # the lid drives the cavity
+    assert abs(R.sum() - R.size) < 1e-4                          # mass
+    assert np.abs(T[4:-4, 4:-4] - 10).max() < 1e-2               # uniform temperature away from the walls
+    dev = np.abs(T - 10)
+    assert np.unravel_index(dev.argmax(), dev.shape)[0] >= T.shape[0] - 2    # what deviation there is sits at the lid
