@@ -508,6 +508,11 @@ typedef base_t storage_t;
     A(f"constexpr int ZONE_SHIFT={m.zone_shift}, ZONE_MAX={m.zone_max};")
     A(f"constexpr int GX={gx}, GY={gy}, GZ={gz};")
     A("constexpr int NO_CUT = 65535, CUT_MAX = 1000; // cut distances are uint16 (reference src/types.h:25-29)")
+    if "cut_t" in m.code or "CUT_LEN" in m.code:
+        # the type and the length macro of the reference's cut distances (src/types.h:25,29); a cut is the fraction of the link
+        # times CUT_MAX here as there (the scale itself is this build's own: host side csrc/host/geometry.cpp calc_cut)
+        A("typedef uint16_t cut_t;")
+        A("#define CUT_LEN(x__) ((1.0f / CUT_MAX) * (x__))")
     for k, v in m.options.items():
         if v:
             A(f"#define OPTIONS_{k} {int(v) if not isinstance(v, bool) else 1}")

@@ -173,3 +173,54 @@ def test_cm_cht_cavity_keeps_a_uniform_temperature(reference_dir, built, tmp_pat
     assert np.abs(T[4:-4, 4:-4] - 10).max() < 1e-2               # uniform temperature away from the walls
     dev = np.abs(T - 10)
     assert np.unravel_index(dev.argmax(), dev.shape)[0] >= T.shape[0] - 2    # what deviation there is sits at the lid
+
+
+def _write_cylinder_stl(path, r, z0, z1, n=96):
+    """binary STL of a closed cylinder around the z axis.  A ray that passes through a vertex (within float rounding) is a hit
+    or a miss by rounding, in the reference's cut search as in this one (src/Geometry.cpp.Rt:479-503), so the polygon is turned
+    away from the lattice directions."""
+    import math
+    import struct
+    tris = []
+    for i in range(n):
+        a0, a1 = 2 * math.pi * (i + 0.37) / n, 2 * math.pi * (i + 1.37) / n      # no vertex on a lattice line or diagonal through the axis
+        p0, p1 = (r * math.cos(a0), r * math.sin(a0)), (r * math.cos(a1), r * math.sin(a1))
+        tris += [((p0[0], p0[1], z0), (p1[0], p1[1], z0), (p1[0], p1[1], z1)), ((p0[0], p0[1], z0), (p1[0], p1[1], z1), (p0[0], p0[1], z1)),
+                 ((0, 0, z0), (p1[0], p1[1], z0), (p0[0], p0[1], z0)), ((0, 0, z1), (p0[0], p0[1], z1), (p1[0], p1[1], z1))]
+    with open(path, "wb") as f:
+        f.write(b"cylinder".ljust(80, b" "))
+        f.write(struct.pack("<I", len(tris)))
+        for t in tris:
+            f.write(struct.pack("<3f", 0, 0, 0))
+            for p in t:
+                f.write(struct.pack("<3f", *p))
+            f.write(struct.pack("<H", 0))
+
+
+def test_cm_cht_3d_heated_cylinder_with_interpolated_bounce_back(reference_dir, built, tmp_path, monkeypatch):
+    """heat/d3q27q7_cm_cht built with the options its example names (OutFlowNeumann, AVG, IBB; the node code declares `cut_t`
+    variables) on example/heat/d3q27q7_Hot_Karman_Re100_Pr5.xml: wall cuts from an STL surface (the example's STL is not in the
+    tree, a cylinder of the same size is written here), interpolated bounce-back for both lattices, Dirichlet temperature on the
+    cylinder.  The temperature obeys the maximum principle between inflow (10) and cylinder (11) and the wake warms up."""
+    import re
+    from tclb_b200 import build
+    from tclb_b200.solver import Solver
+    build.build_from_dir(os.path.join(reference_dir, "models/heat/d3q27q7_cm_cht"), precision="double", options={"OutFlowNeumann": True, "AVG": True, "IBB": True})
+    os.makedirs(tmp_path / "example" / "heat")
+    _write_cylinder_stl(tmp_path / "example" / "heat" / "cylinder_XYplane_D10_Z9.stl", 5.0, -1.0, 9.0)
+    xml = open(os.path.join(reference_dir, "example/heat/d3q27q7_Hot_Karman_Re100_Pr5.xml")).read()
+    xml = xml[xml.index("<?xml"):]
+    xml = re.sub(r'<Solve Iterations="3">.*?</Solve>', '', xml, flags=re.S)
+    xml = re.sub(r'<Solve Iterations="30000">.*?</Solve>', '<Solve Iterations="800"/>', xml, flags=re.S)
+    xml = xml.replace('Failcheck Iterations="5000"', 'Failcheck Iterations="100"')
+    monkeypatch.chdir(tmp_path)
+    s = Solver("ref_d3q27q7_cm_cht_OutFlowNeumann_AVG_IBB", "double", "cpu")
+    s.load_string(xml, "hk").run()
+    T, U, R = (np.asarray(s.Quantities[k]) for k in ("T", "U", "Rho"))
+    s.close()
+    assert T.shape == (3, 100, 512) and np.isfinite(T).all()
+    assert 9.9 < T.min() and T.max() < 11.1 and T.max() > 10.9           # maximum principle (small overshoot of the scheme)
+    assert abs(R.mean() - 1) < 5e-3 and 0.03 < U[..., 0].max() < 0.06     # inflow 0.025 accelerates around the cylinder
+    assert T[1, 45:56, 152:170].mean() > 10.05                           # the wake right behind the cylinder (x 120..150) is heated
+    assert abs(T[1, 5:15, 300:500].mean() - 10) < 5e-3                   # far away nothing has arrived yet
+    assert np.abs(T[0] - T[2]).max() < 1e-9                              # the case is uniform along z
