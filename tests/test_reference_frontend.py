@@ -197,11 +197,7 @@ def _write_cylinder_stl(path, r, z0, z1, n=96):
             f.write(struct.pack("<H", 0))
 
 
-def test_cm_cht_3d_heated_cylinder_with_interpolated_bounce_back(reference_dir, built, tmp_path, monkeypatch):
-    """heat/d3q27q7_cm_cht built with the options its example names (OutFlowNeumann, AVG, IBB; the node code declares `cut_t`
-    variables) on example/heat/d3q27q7_Hot_Karman_Re100_Pr5.xml: wall cuts from an STL surface (the example's STL is not in the
-    tree, a cylinder of the same size is written here), interpolated bounce-back for both lattices, Dirichlet temperature on the
-    cylinder.  The temperature obeys the maximum principle between inflow (10) and cylinder (11) and the wake warms up."""
+def _hot_karman(reference_dir, tmp_path, monkeypatch, backend, iterations=800):
     import re
     from tclb_b200 import build
     from tclb_b200.solver import Solver
@@ -211,16 +207,72 @@ def test_cm_cht_3d_heated_cylinder_with_interpolated_bounce_back(reference_dir, 
     xml = open(os.path.join(reference_dir, "example/heat/d3q27q7_Hot_Karman_Re100_Pr5.xml")).read()
     xml = xml[xml.index("<?xml"):]
     xml = re.sub(r'<Solve Iterations="3">.*?</Solve>', '', xml, flags=re.S)
-    xml = re.sub(r'<Solve Iterations="30000">.*?</Solve>', '<Solve Iterations="800"/>', xml, flags=re.S)
+    xml = re.sub(r'<Solve Iterations="30000">.*?</Solve>', '<Solve Iterations="%d"/>' % iterations, xml, flags=re.S)
     xml = xml.replace('Failcheck Iterations="5000"', 'Failcheck Iterations="100"')
     monkeypatch.chdir(tmp_path)
-    s = Solver("ref_d3q27q7_cm_cht_OutFlowNeumann_AVG_IBB", "double", "cpu")
+    s = Solver("ref_d3q27q7_cm_cht_OutFlowNeumann_AVG_IBB", "double", backend)
     s.load_string(xml, "hk").run()
     T, U, R = (np.asarray(s.Quantities[k]) for k in ("T", "U", "Rho"))
     s.close()
+    return T, U, R
+
+
+def test_cm_cht_3d_heated_cylinder_with_interpolated_bounce_back(reference_dir, built, tmp_path, monkeypatch):
+    """heat/d3q27q7_cm_cht built with the options its example names (OutFlowNeumann, AVG, IBB; the node code declares `cut_t`
+    variables) on example/heat/d3q27q7_Hot_Karman_Re100_Pr5.xml: wall cuts from an STL surface (the example's STL is not in the
+    tree, a cylinder of the same size is written here), interpolated bounce-back for both lattices, Dirichlet temperature on the
+    cylinder.  The temperature obeys the maximum principle between inflow (10) and cylinder (11) and the wake warms up."""
+    T, U, R = _hot_karman(reference_dir, tmp_path, monkeypatch, "cpu")
     assert T.shape == (3, 100, 512) and np.isfinite(T).all()
     assert 9.9 < T.min() and T.max() < 11.1 and T.max() > 10.9           # maximum principle (small overshoot of the scheme)
     assert abs(R.mean() - 1) < 5e-3 and 0.03 < U[..., 0].max() < 0.06     # inflow 0.025 accelerates around the cylinder
     assert T[1, 45:56, 152:170].mean() > 10.05                           # the wake right behind the cylinder (x 120..150) is heated
     assert abs(T[1, 5:15, 300:500].mean() - 10) < 5e-3                   # far away nothing has arrived yet
     assert np.abs(T[0] - T[2]).max() < 1e-9                              # the case is uniform along z
+
+
+HEATED_CYLINDER = """<?xml version="1.0"?>
+<CLBConfig version="2.0" output="output/">
+  <Geometry nx="192" ny="64" nz="3">
+    <CM><Box/></CM>
+    <WVelocity name="Inlet"><Box nx="1"/></WVelocity>
+    <ENeumann name="Outlet"><Box dx="-1"/></ENeumann>
+    <HydroIBB><STL file="cyl.stl" scale="2.0" x="60.3" y="32.2" z="0" side="surface"/></HydroIBB>
+    <HeaterDirichletTemperatureIABB name="Hot"><STL file="cyl.stl" scale="2.0" x="60.3" y="32.2" z="0" side="surface"/></HeaterDirichletTemperatureIABB>
+  </Geometry>
+  <Model>
+    <Param name="InitTemperature" value="10"/>
+    <Param name="InitTemperature" value="10" zone="Inlet"/>
+    <Param name="InitTemperature" value="11" zone="Hot"/>
+    <Param name="nu" value="0.02"/><Param name="conductivity" value="0.01"/>
+    <Param name="nu_buffer" value="0.166666"/><Param name="conductivity_buffer" value="0.166666"/>
+    <Param name="h_stability_enhancement" value="1."/><Param name="cp" value="1."/><Param name="material_density" value="1."/>
+    <Param name="VelocityX" value="0.03"/>
+  </Model>
+  <Solve Iterations="300"/>
+</CLBConfig>
+"""
+
+
+@pytest.mark.gpu
+def test_cm_cht_3d_heated_cylinder_gpu_matches_cpu(built, tmp_path, monkeypatch):
+    """d3q27q7_cm_cht (OutFlowNeumann, AVG, IBB) on the GPU - wall cuts in device memory, interpolated bounce-back of both
+    lattices inside the fused stage kernel - against the CPU oracle of the same generated code.  The library is the one the CPU
+    test builds from the reference's directory; the case is this repository's own, so the test also runs where the reference
+    tree is not mounted."""
+    from tclb_b200.runtime import LIBDIR
+    from tclb_b200.solver import Solver
+    name = "ref_d3q27q7_cm_cht_OutFlowNeumann_AVG_IBB"
+    if not (LIBDIR / f"libtclb_{name}_double.so").exists():
+        pytest.skip("library not built (tests/test_reference_frontend.py builds it where the reference tree is mounted)")
+    _write_cylinder_stl(tmp_path / "cyl.stl", 5.0, -1.0, 9.0)
+    monkeypatch.chdir(tmp_path)
+    out = {}
+    for backend in ("cpu", "cuda"):
+        s = Solver(name, "double", backend)
+        s.load_string(HEATED_CYLINDER, "hc_" + backend).run()
+        out[backend] = [np.asarray(s.Quantities[k]) for k in ("T", "U", "Rho")]
+        s.close()
+    (Tc, Uc, Rc), (Tg, Ug, Rg) = out["cpu"], out["cuda"]
+    assert Tc.max() > 10.9 and Tc.min() > 9.9 and Tc[1, 28:37, 75:90].mean() > 10.01
+    assert np.abs(Tg - Tc).max() < 1e-9 and np.abs(Ug - Uc).max() < 1e-10 and np.abs(Rg - Rc).max() < 1e-10
